@@ -1,0 +1,60 @@
+"""Shared test utilities: golden loading, case table, tolerances (north_star: final parameters
+<= 1e-9 relative in fp64, <= 1e-4 in fp32; identical iteration counts except at tolerance
+boundaries, which are reported)."""
+import os
+
+import numpy as np
+import torch
+
+from conftest import GOLDEN
+
+RTOL = {'f64': 1e-9, 'f32': 1e-4}
+DT = {'f64': torch.float64, 'f32': torch.float32}
+TOL = dict(ftol=1e-8, ptol=1e-8, gtol=1e-8)
+
+# mirrors tests/golden/make_golden.py::CASES (solver name, kwargs)
+CASES = {
+    'lma_lev':  ('lma', dict(meth='lev', max_iter=99, **TOL)),
+    'lma_marq': ('lma', dict(meth='marq', max_iter=99, **TOL)),
+    'gna':      ('gna', dict(l=1., max_iter=99, **TOL)),
+    'gna_l05':  ('gna', dict(l=.5, max_iter=99, **TOL)),
+    'gda':      ('gda', dict(l=1., max_iter=99, **TOL)),
+    'gda_l05':  ('gda', dict(l=.5, max_iter=99, **TOL)),
+}
+PLAIN = {'gna_plain': ('gna_plain', dict(l=.1, max_iter=25)),
+         'gda_plain': ('gda_plain', dict(l=.1, max_iter=25))}
+
+
+def load(name):
+    return dict(np.load(os.path.join(GOLDEN, name + '.npz')))
+
+
+def rel_err(a, b):
+    """max over problems of ||a-b|| / ||b|| (row-wise, parameters as a vector)."""
+    a, b = torch.as_tensor(a).double(), torch.as_tensor(b).double()
+    num = (a - b).norm(dim=-1)
+    den = b.norm(dim=-1).clamp_min(1e-300)
+    return float((num / den).max())
+
+
+def compare_plist(got, want, dn, what, allow_boundary=False):
+    """got: list/stack of [B,P] snapshots; want: golden [K,B,P].  Checks iteration count and
+    EVERY snapshot (not only the last)."""
+    want = torch.as_tensor(want)
+    got = torch.stack(list(got)) if not torch.is_tensor(got) else got
+    got = got.cpu()
+    if got.shape[0] != want.shape[0]:
+        msg = f'{what}: iteration count {got.shape[0]} != reference {want.shape[0]}'
+        if allow_boundary:
+            print('BOUNDARY FLIP:', msg)
+            k = min(got.shape[0], want.shape[0])
+            got, want = got[:k], want[:k]
+        else:
+            raise AssertionError(msg)
+    finite = torch.isfinite(want)
+    assert torch.equal(torch.isfinite(got), finite), f'{what}: finite pattern differs'
+    g = torch.where(finite, got.double(), torch.zeros((), dtype=torch.float64))
+    w = torch.where(finite, want.double(), torch.zeros((), dtype=torch.float64))
+    e = rel_err(g, w)
+    assert e <= RTOL[dn], f'{what}: rel err {e:.3e} > {RTOL[dn]:.0e}'
+    return e

@@ -1,0 +1,124 @@
+"""CPU: pins the oracle (oracle/nlls_oracle.py, oracle/models.py) to golden vectors produced by
+the unmodified reference (tests/golden/make_golden.py)."""
+import pytest
+import torch
+
+from helpers import CASES, PLAIN, DT, load, compare_plist, rel_err
+from oracle import nlls_oracle as O
+from oracle import models as M
+
+
+def _emg_args(gold, dt, n_costs=None):
+    t, y = torch.as_tensor(gold['t']).to(dt), torch.as_tensor(gold['y']).to(dt)
+    fun = lambda p, t, y: M.emg_cost(p, t, y, n_costs=n_costs)
+    jac = lambda p, t, y: M.emg_jac(p, t, y, n_costs=n_costs)
+    return fun, jac, (t, y)
+
+
+@pytest.fixture(scope='module')
+def fixtures():
+    return load('fixtures')
+
+
+@pytest.fixture(scope='module')
+def synthetic():
+    return load('synthetic')
+
+
+@pytest.fixture(scope='module')
+def skew():
+    return load('skewgauss')
+
+
+def _run_case(gold, name, dn, fun, jac, args, prefix=''):
+    key = f'{prefix}{name}__{dn}'
+    dt = DT[dn]
+    solver, kw = CASES[name]
+    p = torch.as_tensor(gold[prefix + 'p0']).to(dt).clone()
+    w = torch.as_tensor(gold.get('wvec', [1.])).to(dt)
+    if key + '__raises' in gold:
+        pytest.skip('reference raises on this input (Marquardt overflow, Q6)')
+    tr = getattr(O, solver)(p, fun, jac, args=args, wvec=w, **kw)
+    assert torch.equal(tr.p_list[-1], p), 'oracle must mutate p in place like the reference (Q1)'
+    return compare_plist(tr.p_list, gold[key + '__plist'], dn, key, allow_boundary=(dn == 'f32'))
+
+
+@pytest.mark.parametrize('dn', ['f64', 'f32'])
+@pytest.mark.parametrize('name', list(CASES))
+def test_fixture_cases(fixtures, name, dn):
+    fun, jac, args = _emg_args(fixtures, DT[dn], n_costs=2)
+    _run_case(fixtures, name, dn, fun, jac, args)
+
+
+@pytest.mark.parametrize('dn', ['f64', 'f32'])
+@pytest.mark.parametrize('name', list(CASES))
+def test_synthetic_cases(synthetic, name, dn):
+    fun, jac, args = _emg_args(synthetic, DT[dn])
+    _run_case(synthetic, name, dn, fun, jac, args)
+
+
+@pytest.mark.parametrize('dn', ['f64', 'f32'])
+@pytest.mark.parametrize('name', ['lma_lev', 'gna', 'gda'])
+@pytest.mark.parametrize('P', [4, 5])
+def test_skewgauss_cases(skew, name, dn, P):
+    dt = DT[dn]
+    pre = f'P{P}_'
+    args = (torch.as_tensor(skew[pre + 'x']).to(dt), torch.as_tensor(skew[pre + 'y']).to(dt))
+    _run_case(skew, name, dn, M.skewgauss_cost, M.skewgauss_jac, args, prefix=pre)
+
+
+@pytest.mark.parametrize('dn', ['f64', 'f32'])
+@pytest.mark.parametrize('name', list(PLAIN))
+def test_plain_variants(fixtures, name, dn):
+    dt = DT[dn]
+    fun, jac, args = _emg_args(fixtures, dt, n_costs=2)
+    solver, kw = PLAIN[name]
+    p = torch.as_tensor(fixtures['p0']).to(dt).clone()
+    w = torch.ones(2, dtype=dt)
+    res = getattr(O, solver)(p, lambda q: fun(q, *args), lambda q: jac(q, *args), w, **kw)
+    assert rel_err(res, fixtures[f'{name}__{dn}__p']) <= (1e-12 if dn == 'f64' else 1e-5)
+
+
+@pytest.mark.parametrize('gname', ['fixtures', 'synthetic'])
+@pytest.mark.parametrize('dn', ['f64', 'f32'])
+def test_normal_equations(gname, dn, fixtures, synthetic):
+    gold = fixtures if gname == 'fixtures' else synthetic
+    dt = DT[dn]
+    fun, jac, args = _emg_args(gold, dt, n_costs=2 if gname == 'fixtures' else None)
+    p = torch.as_tensor(gold['p0']).to(dt)
+    w = torch.as_tensor(gold['wvec']).to(dt)
+    f, J = fun(p, *args), jac(p, *args)
+    g, H = O.normal_equations(f, J, w)
+    tol = 1e-13 if dn == 'f64' else 1e-5
+    assert torch.allclose(f, torch.as_tensor(gold[f'newton__{dn}__f']), rtol=tol, atol=0)
+    assert rel_err(g, gold[f'newton__{dn}__g']) <= tol
+    assert rel_err(H.flatten(1), torch.as_tensor(gold[f'newton__{dn}__H']).flatten(1)) <= tol
+
+
+def test_autograd_jacobian_path(fixtures):
+    """jac_function=None (functions/jacobian.py:36-57) with the reference tests' 1e-5 tolerances."""
+    dt = torch.float64
+    fun, _, args = _emg_args(fixtures, dt, n_costs=2)
+    p = torch.as_tensor(fixtures['p0']).clone()
+    tr = O.lma(p, fun, None, args=args, wvec=torch.ones(2, dtype=dt), ftol=1e-5, ptol=1e-5, gtol=1e-5,
+               meth='lev', max_iter=99)
+    compare_plist(tr.p_list, fixtures['lma_lev_autojac__f64__plist'], 'f64', 'lma_lev_autojac')
+
+
+def test_skewgauss_jacobian_matches_autograd(skew):
+    for P in (4, 5):
+        pre = f'P{P}_'
+        x, y = torch.as_tensor(skew[pre + 'x']), torch.as_tensor(skew[pre + 'y'])
+        p = torch.as_tensor(skew[pre + 'p0'])[:4].clone()
+        Ja = O.autograd_batch_jacobian(p, lambda q: M.skewgauss_cost(q, x, y[:4]))
+        Jm = M.skewgauss_jac(p, x, y[:4])
+        assert torch.allclose(Ja, Jm, rtol=1e-10, atol=1e-12)
+
+
+def test_reference_reaches_ground_truth(fixtures):
+    """The reference's own (loose) assertions: tests/unit_test_parallel.py:254-260."""
+    last = torch.as_tensor(fixtures['lma_lev__f64__plist'][-1])
+    assert torch.allclose(last, torch.as_tensor(fixtures['gt']), atol=1e-1)
+    assert fixtures['lma_lev__f64__plist'].shape[0] < 100
+    # Q6: Marquardt scaling stops after 3 iterations far from the optimum
+    assert fixtures['lma_marq__f64__plist'].shape[0] == 3

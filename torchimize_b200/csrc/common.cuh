@@ -1,0 +1,283 @@
+// common.cuh — shared device/host helpers for the sm_100a NLLS kernels.
+#pragma once
+#include <cuda_runtime.h>
+#include <cstdint>
+#include <cstdio>
+#include "../../include/nlls_b200.h"
+
+#ifndef NLLS_MAX_P
+#define NLLS_MAX_P 32
+#endif
+
+namespace nlls {
+
+// ----------------------------------------------------------------------------- host side
+void set_error(const char* fmt, ...);
+
+inline int check_launch(const char* what) {
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) {
+    set_error("%s: %s", what, cudaGetErrorString(e));
+    return (int)e;
+  }
+  return 0;
+}
+
+inline bool aligned_to(const void* p, size_t a) { return (reinterpret_cast<uintptr_t>(p) % a) == 0; }
+
+constexpr int kNumSMs = 148;   // B200: 2 dies x 74 SMs; grids are sized in multiples of this
+
+// --------------------------------------------------------------------------- device side
+__device__ __forceinline__ bool is_done(const nlls_ctrl* ctrl) {
+  // written by nlls_iter_end in an earlier launch on the same stream: a plain load suffices
+  return ctrl != nullptr && *reinterpret_cast<const volatile int*>(&ctrl->done) != 0;
+}
+__device__ __forceinline__ int iter_index(const nlls_ctrl* ctrl) {
+  return ctrl ? *reinterpret_cast<const volatile int*>(&ctrl->iters) : 0;
+}
+
+template <typename T> __device__ __forceinline__ T shfl_xor(T v, int m) { return __shfl_xor_sync(0xffffffffu, v, m); }
+template <typename T> __device__ __forceinline__ T shfl_down(T v, int d) { return __shfl_down_sync(0xffffffffu, v, d); }
+
+template <typename T> __device__ __forceinline__ T warp_sum(T v) {
+#pragma unroll
+  for (int m = 16; m > 0; m >>= 1) v += shfl_xor(v, m);
+  return v;
+}
+
+// Sum V values held by every lane of a warp; returns in lane 0..(all lanes) the totals.
+// Recursive halving ("transpose reduce"): ~V + 5 shuffles instead of 5 V.  After the call
+// lane L holds the total of value index (L % Vp) where Vp = V rounded up to a power of two
+// <= 32; callers read totals through the returned owner mapping:  total of value k sits in
+// out[0] of lane k (k < V).  For V > 32 falls back to plain butterflies.
+template <int V, typename T>
+__device__ __forceinline__ void warp_sum_many(T (&v)[V]) {
+#pragma unroll
+  for (int k = 0; k < V; ++k) v[k] = warp_sum(v[k]);
+}
+
+// streaming (read-once) global loads: bypass L1 allocation
+__device__ __forceinline__ double ldg_stream(const double* p) {
+  double r;
+  asm volatile("ld.global.nc.L1::no_allocate.f64 %0, [%1];" : "=d"(r) : "l"(p));
+  return r;
+}
+__device__ __forceinline__ float ldg_stream(const float* p) {
+  float r;
+  asm volatile("ld.global.nc.L1::no_allocate.f32 %0, [%1];" : "=f"(r) : "l"(p));
+  return r;
+}
+__device__ __forceinline__ double2 ldg_stream2(const double* p) {
+  double2 r;
+  asm volatile("ld.global.nc.L1::no_allocate.v2.f64 {%0,%1}, [%2];" : "=d"(r.x), "=d"(r.y) : "l"(p));
+  return r;
+}
+__device__ __forceinline__ float4 ldg_stream4(const float* p) {
+  float4 r;
+  asm volatile("ld.global.nc.L1::no_allocate.v4.f32 {%0,%1,%2,%3}, [%4];"
+               : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w) : "l"(p));
+  return r;
+}
+__device__ __forceinline__ float2 ldg_stream2(const float* p) {
+  float2 r;
+  asm volatile("ld.global.nc.L1::no_allocate.v2.f32 {%0,%1}, [%2];" : "=f"(r.x), "=f"(r.y) : "l"(p));
+  return r;
+}
+// streaming stores (written once, read by a later kernel)
+__device__ __forceinline__ void stg_stream(double* p, double v) {
+  asm volatile("st.global.L1::no_allocate.f64 [%0], %1;" ::"l"(p), "d"(v) : "memory");
+}
+__device__ __forceinline__ void stg_stream(float* p, float v) {
+  asm volatile("st.global.L1::no_allocate.f32 [%0], %1;" ::"l"(p), "f"(v) : "memory");
+}
+
+// ---------------------------------------------------------------- mbarrier / bulk-copy (TMA)
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_fence_init() {
+  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "WAIT_LOOP:\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+      "@p bra DONE;\n\t"
+      "bra WAIT_LOOP;\n\t"
+      "DONE:\n\t"
+      "}" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+// 1-D bulk async copy global -> shared, completion signalled on an mbarrier (SASS: UBLKCP).
+// dst, src 16-byte aligned; bytes a multiple of 16.
+__device__ __forceinline__ void bulk_g2s(void* dst_smem, const void* src_gmem, uint32_t bytes, uint64_t* bar) {
+  asm volatile(
+      "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(dst_smem)),
+      "l"(src_gmem), "r"(bytes), "r"(smem_u32(bar))
+      : "memory");
+}
+
+// ------------------------------------------------------------------ small dense fp64 solves
+// Solve A x = b for a symmetric P x P system held fully in registers (A is destroyed).
+// Cholesky first; if a pivot is not strictly positive (or not finite) the original matrix is
+// re-solved by LU with partial pivoting.  Returns false when LU meets an exactly zero /
+// non-finite pivot (result then carries inf/NaN, like an unpivoted QR would).
+template <int P>
+__device__ __forceinline__ bool spd_solve(const double (&A0)[P][P], const double (&b0)[P], double (&x)[P]) {
+  double L[P][P];
+  bool ok = true;
+#pragma unroll
+  for (int j = 0; j < P; ++j) {
+    double d = A0[j][j];
+#pragma unroll
+    for (int k = 0; k < j; ++k) d -= L[j][k] * L[j][k];
+    ok = ok && (d > 0.0) && (d < __longlong_as_double(0x7ff0000000000000LL));
+    const double dj = sqrt(d);
+    L[j][j] = dj;
+    const double inv = 1.0 / dj;
+#pragma unroll
+    for (int i = j + 1; i < P; ++i) {
+      double s = A0[i][j];
+#pragma unroll
+      for (int k = 0; k < j; ++k) s -= L[i][k] * L[j][k];
+      L[i][j] = s * inv;
+    }
+  }
+  if (ok) {
+    double yv[P];
+#pragma unroll
+    for (int i = 0; i < P; ++i) {
+      double s = b0[i];
+#pragma unroll
+      for (int k = 0; k < i; ++k) s -= L[i][k] * yv[k];
+      yv[i] = s / L[i][i];
+    }
+#pragma unroll
+    for (int i = P - 1; i >= 0; --i) {
+      double s = yv[i];
+#pragma unroll
+      for (int k = i + 1; k < P; ++k) s -= L[k][i] * x[k];
+      x[i] = s / L[i][i];
+    }
+    return true;
+  }
+  // ---- LU with partial pivoting (rare path; kept out of the unrolled fast path's way)
+  double A[P][P], b[P];
+#pragma unroll
+  for (int i = 0; i < P; ++i) {
+    b[i] = b0[i];
+#pragma unroll
+    for (int j = 0; j < P; ++j) A[i][j] = A0[i][j];
+  }
+  bool nonsing = true;
+#pragma unroll
+  for (int k = 0; k < P; ++k) {
+    int piv = k;
+    double best = fabs(A[k][k]);
+#pragma unroll
+    for (int i = k + 1; i < P; ++i) {
+      const double a = fabs(A[i][k]);
+      if (a > best) { best = a; piv = i; }
+    }
+#pragma unroll
+    for (int i = k + 1; i < P; ++i) {
+      if (i == piv) {
+#pragma unroll
+        for (int j = 0; j < P; ++j) { const double t = A[k][j]; A[k][j] = A[i][j]; A[i][j] = t; }
+        const double t = b[k]; b[k] = b[i]; b[i] = t;
+      }
+    }
+    const double d = A[k][k];
+    nonsing = nonsing && (d != 0.0) && (fabs(d) < __longlong_as_double(0x7ff0000000000000LL));
+    const double inv = 1.0 / d;
+#pragma unroll
+    for (int i = k + 1; i < P; ++i) {
+      const double m = A[i][k] * inv;
+#pragma unroll
+      for (int j = k + 1; j < P; ++j) A[i][j] -= m * A[k][j];
+      b[i] -= m * b[k];
+    }
+  }
+#pragma unroll
+  for (int i = P - 1; i >= 0; --i) {
+    double s = b[i];
+#pragma unroll
+    for (int k = i + 1; k < P; ++k) s -= A[i][k] * x[k];
+    x[i] = s / A[i][i];
+  }
+  return nonsing;
+}
+
+// Runtime-P variant working on a caller-provided scratch matrix (shared/local memory),
+// row-major with leading dimension ld and element stride `es` (for interleaved layouts).
+__device__ inline bool spd_solve_rt(int P, double* A, int ld, int es, double* b, double* x, double* Awork) {
+  // copy for LU fallback
+  for (int i = 0; i < P; ++i)
+    for (int j = 0; j < P; ++j) Awork[(i * ld + j) * es] = A[(i * ld + j) * es];
+  bool ok = true;
+  const double INF = __longlong_as_double(0x7ff0000000000000LL);
+  for (int j = 0; j < P; ++j) {        // in-place Cholesky, lower triangle of A
+    double d = A[(j * ld + j) * es];
+    for (int k = 0; k < j; ++k) { const double l = A[(j * ld + k) * es]; d -= l * l; }
+    ok = ok && (d > 0.0) && (d < INF);
+    const double dj = sqrt(d);
+    A[(j * ld + j) * es] = dj;
+    const double inv = 1.0 / dj;
+    for (int i = j + 1; i < P; ++i) {
+      double s = A[(i * ld + j) * es];
+      for (int k = 0; k < j; ++k) s -= A[(i * ld + k) * es] * A[(j * ld + k) * es];
+      A[(i * ld + j) * es] = s * inv;
+    }
+  }
+  if (ok) {
+    for (int i = 0; i < P; ++i) {
+      double s = b[i * es];
+      for (int k = 0; k < i; ++k) s -= A[(i * ld + k) * es] * x[k * es];
+      x[i * es] = s / A[(i * ld + i) * es];
+    }
+    for (int i = P - 1; i >= 0; --i) {
+      double s = x[i * es];
+      for (int k = i + 1; k < P; ++k) s -= A[(k * ld + i) * es] * x[k * es];
+      x[i * es] = s / A[(i * ld + i) * es];
+    }
+    return true;
+  }
+  double* M = Awork;
+  bool nonsing = true;
+  for (int k = 0; k < P; ++k) {
+    int piv = k;
+    double best = fabs(M[(k * ld + k) * es]);
+    for (int i = k + 1; i < P; ++i) {
+      const double a = fabs(M[(i * ld + k) * es]);
+      if (a > best) { best = a; piv = i; }
+    }
+    if (piv != k) {
+      for (int j = 0; j < P; ++j) {
+        const double t = M[(k * ld + j) * es]; M[(k * ld + j) * es] = M[(piv * ld + j) * es]; M[(piv * ld + j) * es] = t;
+      }
+      const double t = b[k * es]; b[k * es] = b[piv * es]; b[piv * es] = t;
+    }
+    const double d = M[(k * ld + k) * es];
+    nonsing = nonsing && (d != 0.0) && (fabs(d) < INF);
+    const double inv = 1.0 / d;
+    for (int i = k + 1; i < P; ++i) {
+      const double m = M[(i * ld + k) * es] * inv;
+      for (int j = k + 1; j < P; ++j) M[(i * ld + j) * es] -= m * M[(k * ld + j) * es];
+      b[i * es] -= m * b[k * es];
+    }
+  }
+  for (int i = P - 1; i >= 0; --i) {
+    double s = b[i * es];
+    for (int k = i + 1; k < P; ++k) s -= M[(i * ld + k) * es] * x[k * es];
+    x[i * es] = s / M[(i * ld + i) * es];
+  }
+  return nonsing;
+}
+
+}  // namespace nlls
