@@ -1,0 +1,347 @@
+#!/usr/bin/env python
+"""bench.py — headline benchmark of the batched NLLS hot path on B200.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--path fused|tensor]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
+
+Workload (BASELINE.json configs[1]): lsq_gna_parallel EMG fit, B=65536 problems per GPU, C=5 costs,
+N=1024 residuals, P=4 parameters, fp64, tol 1e-8, max_iter 80 (README.rst:80-84), synthetic data
+(SURVEY.md §8d).  A "step" is ONE full solve of the batch through the public drop-in API
+(torchimize_b200.functions.lsq_gna_parallel); metric = problems solved per second.
+
+  value   whole-job problems/s with inputs resident in HBM (timed with CUDA events, max over ranks)
+  e2e     same call, but every step first copies its inputs (p0, t, y) from pinned host memory and
+          ends with a device->host read of the final parameters
+  roofline  dominant kernel of the timed step, CUDA-event timed per launch in an extra profiled
+          step of the same workload; achieved = algorithmic bytes / average launch duration
+  cpu_baseline  the oracle (CPU restatement of the reference's torch-op path) on a bounded
+          sample of the same workload on the host cores (rank 0, N=1 only)
+
+--impl reference times that oracle port alone on the host cores (the reference is pure Python over
+torch CPU ops and cannot travel to the GPU box; the oracle is its pinned restatement).
+"""
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+import torch                                                     # noqa: E402
+
+WORK = dict(B=65536, C=5, N=1024, P=4, dtype='f64', solver='gna', tol=1e-8, max_iter=80, seed=3008)
+METRIC = 'LM/GN problems solved per second (EMG fits, B x C costs)'
+UNIT = 'problems/s'
+
+
+# ------------------------------------------------------------------------------- data
+def emg_model_t(p, t):
+    """Plain torch EMG model used ONLY to synthesise data (outside every timed region)."""
+    a, mu, s, eta = (p[:, i, None] for i in range(4))
+    d = t - mu
+    return a * torch.exp(-.5 * d ** 2 / s ** 2) * (1 + torch.erf(eta * d / (s * 2 ** .5)))
+
+
+def make_batch(B, C, N, seed, device, dtype):
+    """Seeded synthetic EMG batch: gt = [10,-1,80,5] jittered +-5 %, init = gt
+    jittered +-10 %, y = emg(gt) + 0.01 N(0,1), distinct noise per cost channel."""
+    g = torch.Generator(device=device).manual_seed(seed)
+    base = torch.tensor([10., -1., 80., 5.], dtype=torch.float64, device=device)
+    gt = base * (1 + .1 * (torch.rand(B, 4, generator=g, dtype=torch.float64, device=device) - .5))
+    p0 = gt * (1 + .2 * (torch.rand(B, 4, generator=g, dtype=torch.float64, device=device) - .5))
+    t = torch.linspace(-1e3, 1e3, N, device=device).double()      # built in fp32 then cast (unit_test_parallel.py:42)
+    y = torch.empty(B, C, N, dtype=dtype, device=device)
+    clean = None
+    chunk = 8192
+    for b0 in range(0, B, chunk):
+        clean = emg_model_t(gt[b0:b0 + chunk], t)
+        for c in range(C):
+            noise = torch.randn(clean.shape, generator=g, dtype=torch.float64, device=device)
+            y[b0:b0 + chunk, c] = (clean + .01 * noise).to(dtype)
+    return p0.to(dtype), t.to(dtype), y
+
+
+# ----------------------------------------------------------------------------- clocks
+class ClockSampler(threading.Thread):
+    """Samples SM clock and throttle reasons of one GPU through NVML while the timed region runs."""
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.stop_flag, self.samples, self.reasons, self.max_mhz = index, False, [], set(), None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+        except Exception:                                        # noqa: BLE001
+            self.nv = None
+
+    def run(self):
+        if self.nv is None:
+            return
+        nv = self.nv
+        names = {nv.nvmlClocksThrottleReasonHwSlowdown: 'hw_slowdown',
+                 nv.nvmlClocksThrottleReasonHwThermalSlowdown: 'hw_thermal_slowdown',
+                 nv.nvmlClocksThrottleReasonSwThermalSlowdown: 'sw_thermal_slowdown',
+                 nv.nvmlClocksThrottleReasonSwPowerCap: 'sw_power_cap'}
+        while not self.stop_flag:
+            try:
+                self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                for bit, name in names.items():
+                    if r & bit:
+                        self.reasons.add(name)
+            except Exception:                                    # noqa: BLE001
+                pass
+            time.sleep(0.05)
+
+    def summary(self):
+        s = sorted(self.samples)
+        return {'sm_mhz': (s[len(s) // 2] if s else None), 'sm_max_mhz': self.max_mhz, 'reasons': sorted(self.reasons),
+                'samples': len(s)}
+
+
+# ------------------------------------------------------------------- reference (CPU) arm
+def oracle_solve(B, work, threads):
+    """One GN solve of a B-problem sample of the workload with the oracle on the host cores."""
+    from oracle import nlls_oracle as O, models as M
+    torch.set_num_threads(threads)
+    dt = torch.float64 if work['dtype'] == 'f64' else torch.float32
+    p0, t, y = make_batch(B, work['C'], work['N'], work['seed'], 'cpu', dt)
+    w = torch.ones(work['C'], dtype=dt)
+    t0 = time.perf_counter()
+    tr = O.gna(p0.clone(), M.emg_cost, M.emg_jac, args=(t, y), wvec=w, ftol=work['tol'], ptol=work['tol'], gtol=work['tol'],
+               max_iter=work['max_iter'])
+    dt_s = time.perf_counter() - t0
+    return dt_s, tr.iterations
+
+
+def cpu_baseline(work, budget_s=20.0):
+    threads = os.cpu_count() or 1
+    probe_B = 64
+    s, _ = oracle_solve(probe_B, work, threads)                  # warm-up + cost probe
+    per_problem = s / probe_B
+    B = int(max(64, min(4096, budget_s / max(per_problem, 1e-9))))
+    s, iters = oracle_solve(B, work, threads)
+    return {'value': B / s, 'unit': UNIT, 'cores': threads, 'kind': 'port',
+            'sample': f'oracle GN on the first-seeded {B} of {work["B"]} problems (C={work["C"]},N={work["N"]},P=4,{work["dtype"]}), '
+                      f'{iters} iterations, {s:.1f} s, torch {torch.__version__} CPU, {threads} threads',
+            'iterations': iters}
+
+
+def run_reference(args):
+    rank = int(os.environ.get('RANK', '0'))
+    if rank != 0:
+        return
+    threads = os.cpu_count() or 1
+    work = dict(WORK)
+    s, _ = oracle_solve(64, work, threads)
+    total_budget = 90.0
+    B = int(max(64, min(2048, total_budget / (args.steps + args.warmup) / max(s / 64, 1e-9))))
+    for _ in range(args.warmup):
+        oracle_solve(B, work, threads)
+    times, iters = [], 0
+    for _ in range(args.steps):
+        s, iters = oracle_solve(B, work, threads)
+        times.append(s)
+    tot = sum(times)
+    val = B * args.steps / tot
+    line = {'metric': METRIC, 'value': val, 'unit': UNIT, 'n_gpus': args.gpus, 'steps': args.steps, 'warmup': args.warmup,
+            'ms_per_step': 1e3 * tot / args.steps, 'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None,
+            'dtype': work['dtype'], 'data': 'synthetic', 'impl': 'reference',
+            'config': {'workload': f'lsq_gna_parallel EMG fit, C={work["C"]}, N={work["N"]}, P=4, {work["dtype"]}, tol 1e-8, '
+                                   f'max_iter {work["max_iter"]}; bounded sample of {B} problems per step on host cores',
+                       'iterations': iters},
+            'cpu_baseline': {'value': val, 'unit': UNIT, 'cores': threads, 'kind': 'port',
+                             'sample': f'{B} problems per step, {args.steps} steps'},
+            'e2e': {'value': val, 'unit': UNIT, 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
+            'gpu_launches': 0}
+    print(json.dumps(line), flush=True)
+
+
+# --------------------------------------------------------------------------- our arm
+def run_ours(args):
+    import torch.distributed as dist
+    from torchimize_b200 import _lib
+    from torchimize_b200.functions import lsq_gna_parallel
+    from torchimize_b200.models import EMGModel
+    from torchimize_b200.sharding import gather_results
+
+    world = int(os.environ.get('WORLD_SIZE', '1'))
+    rank = int(os.environ.get('RANK', '0'))
+    local = int(os.environ.get('LOCAL_RANK', '0'))
+    torch.cuda.set_device(local)
+    dev = torch.device('cuda', local)
+    if world > 1:
+        dist.init_process_group('nccl', device_id=dev)
+    work = dict(WORK)
+    if args.B:
+        work['B'] = args.B
+    B, C, N, P = work['B'], work['C'], work['N'], work['P']
+    dt = torch.float64 if work['dtype'] == 'f64' else torch.float32
+    esz = 8 if dt == torch.float64 else 4
+    assert _lib.load().nlls_device_check() == 0, _lib.load().nlls_last_error().decode()
+
+    p0, t, y = make_batch(B, C, N, work['seed'] + 1000 * rank, dev, dt)      # weak scaling: B problems per GPU
+    w = torch.ones(C, dtype=dt, device=dev)
+    emg = EMGModel()
+    fused = args.path == 'fused'
+    tol = work['tol']
+
+    def solve(p, tt, yy):
+        return lsq_gna_parallel(p, emg.cost, emg.jac, args=(tt, yy), wvec=w, ftol=tol, ptol=tol, gtol=tol,
+                                max_iter=work['max_iter'], fused=fused)
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, steps):
+        evs = []
+        barrier()
+        for _ in range(steps):
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            out = fn()
+            b.record()
+            evs.append((a, b))
+        barrier()
+        ms = sum(a.elapsed_time(b) for a, b in evs)
+        tms = torch.tensor([ms], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(tms, op=dist.ReduceOp.MAX)
+        return float(tms.item()), out
+
+    # ---- resident-input steps ("value")
+    p = torch.empty_like(p0)
+    iters_seen = []
+
+    def step_resident():
+        p.copy_(p0)
+        coeffs = solve(p, t, y)
+        iters_seen.append(len(coeffs))
+        if world > 1:
+            gather_results(p, B * world)                         # the one collective of the path (finals)
+        return coeffs
+
+    for _ in range(args.warmup):
+        step_resident()
+    launches0 = _lib.launches
+    sampler = ClockSampler(local)
+    sampler.start()
+    ms_total, coeffs = timed(step_resident, args.steps)
+    launches = _lib.launches - launches0
+    iters = iters_seen[-1]
+
+    # ---- end-to-end steps: host buffers in, host result out
+    hp0, ht, hy = (x.cpu().pin_memory() for x in (p0, t, y))
+    h_out = torch.empty(B, P, dtype=dt).pin_memory()
+    d_p, d_t, d_y = torch.empty_like(p0), torch.empty_like(t), torch.empty_like(y)
+
+    def step_e2e():
+        d_p.copy_(hp0, non_blocking=True)
+        d_t.copy_(ht, non_blocking=True)
+        d_y.copy_(hy, non_blocking=True)
+        coeffs = solve(d_p, d_t, d_y)
+        h_out.copy_(d_p, non_blocking=True)
+        return coeffs
+
+    e2e_steps = max(1, min(args.steps, 3))
+    step_e2e()
+    ms_e2e, _ = timed(step_e2e, e2e_steps)
+    sampler.stop_flag = True
+    sampler.join(timeout=2)
+    h2d = (hp0.numel() + ht.numel() + hy.numel()) * esz
+    d2h = h_out.numel() * esz
+
+    # ---- per-kernel breakdown of one more (profiled) step: CUDA events around every launch
+    _lib.enable_timing(True)
+    p.copy_(p0)
+    n_it = len(solve(p, t, y))
+    recs = _lib.timing_records()
+    _lib.enable_timing(False)
+    per = {}
+    for name, ms in recs:
+        per.setdefault(name, []).append(ms)
+    top_name = 'nlls_model_normal_eq' if fused else None
+    if not fused:
+        tot = {k: sum(v[:n_it]) for k, v in per.items()}
+        top_name = max(tot, key=tot.get)
+    live = per[top_name][:n_it]
+    avg_ms = sum(live) / len(live)
+    step_ms_profiled = sum(sum(v) for v in per.values())
+    share = sum(live) / step_ms_profiled if step_ms_profiled else None
+    if top_name == 'nlls_model_normal_eq':
+        bytes_per_problem = 3 * esz * C * N                      # y read + f_prev read + f write
+        byte_note = 'y + f_prev + f per problem-iteration: 3*s*C*N (SURVEY §8d fused figure s*C*N + stored f_prev traffic)'
+    elif top_name == 'nlls_normal_eq':
+        bytes_per_problem = esz * C * N * (P + 2)                # GN s*C*N*(P+2)
+        byte_note = 'J + f + f_prev per problem-iteration: s*C*N*(P+2) (SURVEY §8d)'
+    else:                                                        # nlls_model_eval: y read, f + J written
+        bytes_per_problem = esz * C * N * (P + 2)
+        byte_note = 'y read + f, J written per problem-iteration: s*C*N*(P+2)'
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, 'MEASURED_PEAKS.json')))
+    except Exception:                                            # noqa: BLE001
+        pass
+    peak = float(peaks.get('hbm_gbs', 6650.0))
+    achieved = bytes_per_problem * B / (avg_ms * 1e-3) / 1e9
+    traffic = None
+    try:
+        traffic = json.load(open(os.path.join(ROOT, 'profiles', 'traffic.json'))).get(top_name)
+    except Exception:                                            # noqa: BLE001
+        pass
+    roof = {'bound': 'hbm', 'kernel': top_name, 'achieved': achieved, 'peak': peak, 'unit': 'GB/s', 'frac': achieved / peak,
+            'traffic': traffic, 'peak_source': 'MEASURED_PEAKS.json hbm_gbs (measured)' if peaks else 'fallback 6650 GB/s',
+            'avg_launch_ms': avg_ms, 'launches_timed': len(live), 'share_of_step': share, 'algorithmic_bytes_per_launch':
+            bytes_per_problem * B, 'bytes_note': byte_note,
+            'kernels_ms_per_step': {k: sum(v[:n_it]) for k, v in per.items()}}
+
+    if rank == 0:
+        val = B * world * args.steps / (ms_total * 1e-3)
+        e2e_val = B * world * e2e_steps / (ms_e2e * 1e-3)
+        line = {'metric': METRIC, 'value': val, 'unit': UNIT, 'n_gpus': world, 'steps': args.steps, 'warmup': args.warmup,
+                'ms_per_step': ms_total / args.steps, 'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None,
+                'dtype': work['dtype'], 'data': 'synthetic',
+                'config': {'workload': f'lsq_gna_parallel EMG fit B={B} per GPU, C={C}, N={N}, P={P}, {work["dtype"]}, tol 1e-8, '
+                                       f'max_iter {work["max_iter"]} (BASELINE.json configs[1])', 'path': args.path,
+                           'iterations': iters, 'problem_iters_per_s': val * iters,
+                           'l2': f'inputs {y.numel() * esz / 1e9:.2f} GB per GPU >> 126 MB L2 (no flush needed)',
+                           'parallelism': f'B sharded over {world} GPU(s), no per-iteration collective, one all-gather of finals'},
+                'e2e': {'value': e2e_val, 'unit': UNIT, 'h2d_bytes_per_step': h2d, 'd2h_bytes_per_step': d2h,
+                        'ms_per_step': ms_e2e / e2e_steps, 'steps': e2e_steps},
+                'gpu_launches': launches, 'roofline': roof, 'clocks': sampler.summary()}
+        if world == 1 and not args.no_cpu_baseline:
+            line['cpu_baseline'] = cpu_baseline(work)
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument('--gpus', type=int, default=1)
+    ap.add_argument('--steps', type=int, default=5)
+    ap.add_argument('--warmup', type=int, default=3)
+    ap.add_argument('--impl', default='ours', choices=['ours', 'reference'])
+    ap.add_argument('--path', default='fused', choices=['fused', 'tensor'])
+    ap.add_argument('--B', type=int, default=0, help='override problems per GPU (debug)')
+    ap.add_argument('--no-cpu-baseline', action='store_true')
+    args = ap.parse_args()
+    if args.impl == 'reference':
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == '__main__':
+    main()

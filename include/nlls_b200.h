@@ -64,6 +64,8 @@ typedef struct nlls_ctrl {
 int nlls_abi_version(void);
 const char* nlls_last_error(void);                 /* host string, thread-local */
 int nlls_device_check(void);                       /* 0 if the current device is sm_100; else NLLS_E_ARCH */
+int nlls_set_force_direct(int on);                 /* test/bench hook: 1 = K1 never takes the bulk-copy staged
+                                                      kernel; returns the previous setting */
 
 /* ---- K1: fused weighted normal equations (tensor path) ------------------------------
  * Replaces newton_parallel.py:40-43 (four einsums; J read twice) and the f re-reads of
@@ -93,8 +95,10 @@ int nlls_cost_stat(int dtype, const void* f, long long B, int C, int N, double* 
                    const nlls_ctrl* ctrl, void* stream);
 
 /* ---- K2: damped solve (lma:96-98) -------------------------------------------------
- * marquardt != 0: dscale[b] *= max_p max(H[b,p,p], dscale[b])   (lma:88, compounding, Q6)
- * Hu = H + u[b]*dscale[b]*I ;  h = -solve_fp64(Hu, g) cast to dtype ;  p_trial = p + h.
+ * marquardt != 0: dscale[b,:] *= max_p max(H[b,p,p], dscale[b,0])   (lma:88, compounding, Q6)
+ * dscale is [B,2]: {diagonal scale, off-diagonal state}; initialise to {1, 0}.  The second entry
+ * reproduces the reference's dense D, whose zeros turn NaN once the scale overflows (0*inf).
+ * Hu = H + u[b]*D ;  h = -solve_fp64(Hu, g) cast to dtype ;  p_trial = p + h.
  * Cholesky in registers, LU with partial pivoting when a pivot is not positive.  */
 int nlls_lm_solve(int dtype, const void* g, const void* H, const void* p, const void* u,
                   void* dscale, int marquardt, long long B, int P,

@@ -1,0 +1,142 @@
+"""ctypes binding of libnlls_b200.so (C ABI: include/nlls_b200.h).  Plumbing only: torch owns
+device memory and streams, the library owns every kernel."""
+import ctypes
+import os
+import subprocess
+import threading
+
+import torch
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, 'libnlls_b200.so')
+CSRC = os.path.join(_HERE, 'csrc')
+
+F32, F64 = 0, 1
+SOLVER_GN, SOLVER_LM, SOLVER_GD = 0, 1, 2
+LM_LEVENBERG, LM_MARQUARDT = 0, 1
+MODEL_EMG, MODEL_SKEWGAUSS = 0, 1
+CTRL_BYTES = 48
+
+_vp, _i, _ll, _d = ctypes.c_void_p, ctypes.c_int, ctypes.c_longlong, ctypes.c_double
+
+# name -> argtypes; mirrors include/nlls_b200.h one to one (tests check the exported symbols)
+SIGNATURES = {
+    'nlls_abi_version': [],
+    'nlls_device_check': [],
+    'nlls_set_force_direct': [_i],
+    'nlls_normal_eq': [_i, _vp, _vp, _vp, _vp, _i, _ll, _i, _i, _i, _vp, _vp, _vp, _vp, _vp],
+    'nlls_normal_eq_gda': [_i, _vp, _vp, _vp, _vp, _i, _ll, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp],
+    'nlls_cost_stat': [_i, _vp, _ll, _i, _i, _vp, _vp, _vp],
+    'nlls_lm_solve': [_i, _vp, _vp, _vp, _vp, _vp, _i, _ll, _i, _vp, _vp, _vp, _vp],
+    'nlls_lm_update': [_i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _d, _d, _d, _d, _d, _d, _d, _ll, _i, _vp, _vp, _vp, _vp],
+    'nlls_gn_update': [_i, _vp, _vp, _vp, _vp, _d, _d, _d, _d, _i, _ll, _i, _vp, _vp, _vp, _vp],
+    'nlls_gd_update': [_i, _vp, _vp, _vp, _vp, _d, _d, _d, _d, _i, _ll, _i, _vp, _vp, _vp, _vp],
+    'nlls_iter_end': [_vp, _i, _d, _vp],
+    'nlls_model_eval': [_i, _i, _vp, _i, _vp, _vp, _ll, _ll, _ll, _i, _i, _vp, _vp, _vp, _vp],
+    'nlls_model_normal_eq': [_i, _i, _vp, _i, _vp, _vp, _ll, _ll, _vp, _i, _ll, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp],
+    'nlls_model_normal_eq_gda': [_i, _i, _vp, _i, _vp, _vp, _ll, _ll, _vp, _i, _ll, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp],
+    'nlls_model_cost_stat': [_i, _i, _vp, _i, _vp, _vp, _ll, _ll, _ll, _i, _i, _vp, _vp, _vp],
+}
+
+_lock = threading.Lock()
+_lib = None
+launches = 0          # kernels enqueued through this binding (bench.py reports it as gpu_launches)
+_LAUNCHES_PER_CALL = {'nlls_gd_update': 2}
+
+
+class NllsError(RuntimeError):
+    pass
+
+
+def build(verbose=False):
+    """Compile csrc/*.cu for sm_100a into libnlls_b200.so (in-tree, next to this file)."""
+    r = subprocess.run(['make', '-C', CSRC, '-j8'], capture_output=True, text=True)
+    if r.returncode != 0:
+        raise NllsError('building libnlls_b200.so failed:\n' + r.stdout[-4000:] + r.stderr[-4000:])
+    if verbose:
+        print(r.stdout[-2000:])
+    return LIB_PATH
+
+
+def load():
+    """Load the library; raises loudly when it is missing (no fallback path exists)."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    with _lock:
+        if _lib is None:
+            if not os.path.exists(LIB_PATH):
+                raise NllsError(f'{LIB_PATH} not found: run `python -c "import __graft_entry__ as g; g.build()"` '
+                                f'or `make -C {CSRC}`; torchimize_b200 has no CPU or torch fallback')
+            lib = ctypes.CDLL(LIB_PATH)
+            for name, argtypes in SIGNATURES.items():
+                fn = getattr(lib, name)
+                fn.argtypes = argtypes
+                fn.restype = _i
+            lib.nlls_last_error.restype = ctypes.c_char_p
+            lib.nlls_last_error.argtypes = []
+            if os.environ.get('NLLS_FORCE_DIRECT') == '1':     # debug: keep K1 off the bulk-copy staged kernel
+                lib.nlls_set_force_direct(1)
+            _lib = lib
+    return _lib
+
+
+def dtype_code(t: torch.Tensor) -> int:
+    if t.dtype == torch.float64:
+        return F64
+    if t.dtype == torch.float32:
+        return F32
+    raise NllsError(f'unsupported dtype {t.dtype}: the B200 core computes in float32 or float64')
+
+
+def ptr(t):
+    return None if t is None else t.data_ptr()
+
+
+def require_cuda(*tensors):
+    for t in tensors:
+        if t is not None and not t.is_cuda:
+            raise NllsError('torchimize_b200 runs on CUDA tensors only (no CPU fallback by design); got a '
+                            f'{t.device} tensor')
+
+
+def stream_ptr():
+    return torch.cuda.current_stream().cuda_stream
+
+
+_timing = None        # when a list: (name, start_event, end_event) per call (bench.py's per-kernel breakdown)
+
+
+def enable_timing(on=True):
+    global _timing
+    _timing = [] if on else None
+
+
+def timing_records():
+    """[(name, milliseconds)] in call order; synchronises."""
+    torch.cuda.synchronize()
+    return [(n, a.elapsed_time(b)) for n, a, b in (_timing or [])]
+
+
+def call(name, *args):
+    """Invoke an entry point on the current stream of the current device; raise on error."""
+    global launches
+    lib = load()
+    if _timing is not None:
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        rc = getattr(lib, name)(*args)
+        b.record()
+        _timing.append((name, a, b))
+    else:
+        rc = getattr(lib, name)(*args)
+    if rc != 0:
+        raise NllsError(f'{name} failed (code {rc}): {lib.nlls_last_error().decode()}')
+    launches += _LAUNCHES_PER_CALL.get(name, 1)
+    return rc
+
+
+def new_ctrl(device):
+    """Zeroed device-resident nlls_ctrl block (48 bytes) as an int32 view + fp64 view."""
+    raw = torch.zeros(CTRL_BYTES // 8, dtype=torch.float64, device=device)
+    return raw

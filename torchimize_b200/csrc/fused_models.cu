@@ -1,0 +1,423 @@
+// fused_models.cu — K4: residual + Jacobian of the built-in models fused into the normal-equation
+// reduction, so that J [B,C,N,P] is never materialised and the iteration is not bound by Python
+// callables (north_star item 4).
+//
+// Per problem b the model (m, k = -dm/dp) is evaluated ONCE per abscissa sample n and shared by
+// all C costs; with r_c = y_c - m:
+//     f_c = r_c^2,  J_c = 2 r_c k
+//     g   = sum_n k   * (2 sum_c w_c r_c^3)
+//     H   = sum_n k k^T (4 sum_c w_c r_c^2)
+// (newton_parallel.py:40-43 applied to tests/unit_test_parallel.py:53-65,105-118).  HBM traffic per
+// iteration: y once, f_prev once (read), f once (write) — 3*s*C*N bytes per problem.
+#include "models.cuh"
+#include "rowacc.cuh"
+
+namespace nlls {
+
+constexpr int kFusedTPB = 128;
+constexpr int kFusedS = 4;       // abscissa samples per thread per tile
+
+template <typename T>
+__device__ __forceinline__ T ld_cached(const T* p) { return __ldg(p); }
+
+// ------------------------------------------------------------------ fused normal equations
+template <typename T, typename Model, int TPB, int S>
+__global__ void __launch_bounds__(TPB)
+k_model_normal_eq(const T* __restrict__ p, const T* __restrict__ x, const T* __restrict__ y, long long ybs,
+                  long long ycs, const T* __restrict__ w, int wlen, long long B, int C, int N, T* fA, T* fB,
+                  T* __restrict__ g, T* __restrict__ H, double* __restrict__ stats, const nlls_ctrl* ctrl) {
+  if (is_done(ctrl)) return;
+  constexpr int P = Model::P, NW = TPB / 32, NH = Tri<P>::N, V = P + NH + 2;
+  const int it = iter_index(ctrl);
+  T* __restrict__ f_out = (it & 1) ? fB : fA;
+  const T* __restrict__ f_prev = (it > 0 && fA) ? ((it & 1) ? fA : fB) : nullptr;
+  extern __shared__ double smem[];
+  double* red = smem;                  // [NW][V]
+  double* sfc = smem + NW * V;         // [C][TPB] per-thread per-cost sums of f
+  double* sfw = sfc + (size_t)C * TPB; // [C][NW]
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+
+  for (long long b = blockIdx.x; b < B; b += gridDim.x) {
+    Model M;
+    M.load(p + b * P);
+    RowAcc<T, P> acc;
+    acc.clear();
+    double sd = 0.0, sq = 0.0;
+    for (int c = 0; c < C; ++c) sfc[c * TPB + tid] = 0.0;
+    const T* yb = y + b * ybs;
+    for (int n0 = 0; n0 < N; n0 += TPB * S) {
+      T m[S], k[S][P], s2[S], s3[S];
+#pragma unroll
+      for (int i = 0; i < S; ++i) {
+        const int n = n0 + i * TPB + tid;
+        M.eval(ld_cached(x + min(n, N - 1)), m[i], k[i]);
+        s2[i] = T(0);
+        s3[i] = T(0);
+      }
+#pragma unroll 2
+      for (int c = 0; c < C; ++c) {
+        const T wc = w[wlen == 1 ? 0 : c];
+        const T* yc = yb + c * ycs;
+        const long long seg = (b * C + c) * (long long)N;
+        double sfl = 0.0;
+#pragma unroll
+        for (int i = 0; i < S; ++i) {
+          const int n = n0 + i * TPB + tid;
+          if (n < N) {
+            const T r = ld_cached(yc + n) - m[i];
+            const T fv = r * r;
+            if (f_out) stg_stream(f_out + seg + n, fv);
+            if (f_prev) {
+              const T d = ldg_stream(f_prev + seg + n) - fv;
+              sd = fma((double)d, (double)d, sd);
+            }
+            sq = fma((double)fv, (double)fv, sq);
+            sfl += (double)fv;
+            const T wf = wc * fv;
+            s2[i] += wf;
+            s3[i] = fma(wf, r, s3[i]);
+          }
+        }
+        sfc[c * TPB + tid] += sfl;
+      }
+#pragma unroll
+      for (int i = 0; i < S; ++i) {
+        const int n = n0 + i * TPB + tid;
+        if (n < N) acc.add_scaled(k[i], T(2) * s3[i], T(4) * s2[i]);
+      }
+    }
+    acc.warp_reduce();
+    sd = warp_sum(sd);
+    sq = warp_sum(sq);
+    for (int c = 0; c < C; ++c) {
+      const double s = warp_sum(sfc[c * TPB + tid]);
+      if (lane == 0) sfw[c * NW + warp] = s;
+    }
+    if (lane == 0) {
+      double* r = red + warp * V;
+#pragma unroll
+      for (int i = 0; i < P; ++i) r[i] = (double)acc.g[i];
+#pragma unroll
+      for (int i = 0; i < NH; ++i) r[P + i] = (double)acc.h[i];
+      r[P + NH] = sd;
+      r[P + NH + 1] = sq;
+    }
+    __syncthreads();
+    if (tid < V) {
+      double s = 0.0;
+#pragma unroll
+      for (int kk = 0; kk < NW; ++kk) s += red[kk * V + tid];
+      if (tid < P) {
+        g[b * P + tid] = (T)s;
+      } else if (tid < P + NH) {
+        int kk = tid - P, i = 0;
+        while (kk >= P - i) { kk -= P - i; ++i; }
+        const int j = i + kk;
+        H[b * P * P + i * P + j] = (T)s;
+        H[b * P * P + j * P + i] = (T)s;
+      } else {
+        stats[b * 4 + (tid - P - NH) + 1] = s;
+      }
+    } else if (tid == V) {
+      double tot = 0.0;
+      for (int c = 0; c < C; ++c) {
+        double s = 0.0;
+        for (int kk = 0; kk < NW; ++kk) s += sfw[c * NW + kk];
+        tot = fma(s, s, tot);
+      }
+      stats[b * 4 + 0] = tot;
+      stats[b * 4 + 3] = 0.0;
+    }
+    __syncthreads();
+  }
+}
+
+// ------------------------------------------------------------------ fused GD flavour
+template <typename T, typename Model, int TPB>
+__global__ void __launch_bounds__(TPB)
+k_model_normal_eq_gda(const T* __restrict__ p, const T* __restrict__ x, const T* __restrict__ y, long long ybs,
+                      long long ycs, const T* __restrict__ w, int wlen, long long B, int C, int N, T* fsA, T* fsB,
+                      double* __restrict__ g64, double* __restrict__ H64, double* __restrict__ stats,
+                      const nlls_ctrl* ctrl) {
+  if (is_done(ctrl)) return;
+  constexpr int P = Model::P, NW = TPB / 32, NH = Tri<P>::N, V = P + NH + 2;
+  const int it = iter_index(ctrl);
+  T* __restrict__ fs_out = (it & 1) ? fsB : fsA;
+  const T* __restrict__ fs_prev = (it > 0 && fsA) ? ((it & 1) ? fsA : fsB) : nullptr;
+  __shared__ double red[NW * V];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  for (long long b = blockIdx.x; b < B; b += gridDim.x) {
+    Model M;
+    M.load(p + b * P);
+    RowAcc<double, P> acc;
+    acc.clear();
+    double sd = 0.0, sq = 0.0;
+    const T* yb = y + b * ybs;
+    for (int n = tid; n < N; n += TPB) {
+      T m, k[P];
+      M.eval(ld_cached(x + n), m, k);
+      T s1 = T(0), fs = T(0);
+      for (int c = 0; c < C; ++c) {
+        const T wc = w[wlen == 1 ? 0 : c];
+        const T r = ld_cached(yb + c * ycs + n) - m;
+        s1 = fma(wc, r, s1);
+        fs = fma(wc, r * r, fs);                               // gda:136
+      }
+      double jd[P];
+#pragma unroll
+      for (int i = 0; i < P; ++i) jd[i] = (double)(T(2) * s1 * k[i]);   // gda:137 (cost-summed row, in T)
+      acc.add(jd, (double)fs, 1.0);
+      if (fs_out) fs_out[b * N + n] = fs;
+      sq = fma((double)fs, (double)fs, sq);
+      if (fs_prev) { const T d = fs_prev[b * N + n] - fs; sd = fma((double)d, (double)d, sd); }
+    }
+    acc.warp_reduce();
+    sd = warp_sum(sd);
+    sq = warp_sum(sq);
+    if (lane == 0) {
+      double* r = red + warp * V;
+#pragma unroll
+      for (int i = 0; i < P; ++i) r[i] = acc.g[i];
+#pragma unroll
+      for (int i = 0; i < NH; ++i) r[P + i] = acc.h[i];
+      r[P + NH] = sd;
+      r[P + NH + 1] = sq;
+    }
+    __syncthreads();
+    if (tid < V) {
+      double s = 0.0;
+#pragma unroll
+      for (int kk = 0; kk < NW; ++kk) s += red[kk * V + tid];
+      if (tid < P) {
+        g64[b * P + tid] = s;
+      } else if (tid < P + NH) {
+        int kk = tid - P, i = 0;
+        while (kk >= P - i) { kk -= P - i; ++i; }
+        const int j = i + kk;
+        H64[b * P * P + i * P + j] = s;
+        H64[b * P * P + j * P + i] = s;
+      } else {
+        stats[b * 4 + (tid - P - NH) + 1] = s;
+      }
+    } else if (tid == V) {
+      stats[b * 4 + 0] = 0.0;
+      stats[b * 4 + 3] = 0.0;
+    }
+    __syncthreads();
+  }
+}
+
+// ------------------------------------------------------------------ fused trial cost (lma:99-100)
+template <typename T, typename Model, int TPB, int S>
+__global__ void __launch_bounds__(TPB)
+k_model_cost_stat(const T* __restrict__ p, const T* __restrict__ x, const T* __restrict__ y, long long ybs,
+                  long long ycs, long long B, int C, int N, double* __restrict__ out, const nlls_ctrl* ctrl) {
+  if (is_done(ctrl)) return;
+  constexpr int P = Model::P, NW = TPB / 32;
+  extern __shared__ double smem[];
+  double* sfc = smem;                  // [C][TPB]
+  double* sfw = sfc + (size_t)C * TPB; // [C][NW]
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  for (long long b = blockIdx.x; b < B; b += gridDim.x) {
+    Model M;
+    M.load(p + b * P);
+    for (int c = 0; c < C; ++c) sfc[c * TPB + tid] = 0.0;
+    const T* yb = y + b * ybs;
+    for (int n0 = 0; n0 < N; n0 += TPB * S) {
+      T m[S];
+#pragma unroll
+      for (int i = 0; i < S; ++i) m[i] = M.value(ld_cached(x + min(n0 + i * TPB + tid, N - 1)));
+      for (int c = 0; c < C; ++c) {
+        const T* yc = yb + c * ycs;
+        double sfl = 0.0;
+#pragma unroll
+        for (int i = 0; i < S; ++i) {
+          const int n = n0 + i * TPB + tid;
+          if (n < N) { const T r = ld_cached(yc + n) - m[i]; sfl += (double)(r * r); }
+        }
+        sfc[c * TPB + tid] += sfl;
+      }
+    }
+    for (int c = 0; c < C; ++c) {
+      const double s = warp_sum(sfc[c * TPB + tid]);
+      if (lane == 0) sfw[c * NW + warp] = s;
+    }
+    __syncthreads();
+    if (tid == 0) {
+      double tot = 0.0;
+      for (int c = 0; c < C; ++c) {
+        double s = 0.0;
+        for (int kk = 0; kk < NW; ++kk) s += sfw[c * NW + kk];
+        tot = fma(s, s, tot);
+      }
+      out[b] = tot;
+    }
+    __syncthreads();
+  }
+}
+
+// ------------------------------------------------------------------ materialising callables
+// thread per (b, n): writes f[b,c,n] and J[b,c,n,:] for every cost c.
+template <typename T, typename Model>
+__global__ void __launch_bounds__(256)
+k_model_eval(const T* __restrict__ p, const T* __restrict__ x, const T* __restrict__ y, long long ybs, long long ycs,
+             long long B, int C, int N, T* __restrict__ f_out, T* __restrict__ J_out, const nlls_ctrl* ctrl) {
+  if (is_done(ctrl)) return;
+  constexpr int P = Model::P;
+  const long long total = B * (long long)N;
+  for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
+       idx += (long long)gridDim.x * blockDim.x) {
+    const long long b = idx / N;
+    const int n = (int)(idx - b * N);
+    Model M;
+    M.load(p + b * P);
+    T m, k[P];
+    if (J_out) M.eval(ld_cached(x + n), m, k);
+    else m = M.value(ld_cached(x + n));
+    for (int c = 0; c < C; ++c) {
+      const T r = ld_cached(y + b * ybs + c * ycs + n) - m;
+      const long long row = (b * C + c) * (long long)N + n;
+      f_out[row] = r * r;
+      if (J_out) {
+        const T c2 = T(2) * r;
+#pragma unroll
+        for (int i = 0; i < P; ++i) J_out[row * P + i] = c2 * k[i];
+      }
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------ dispatch
+template <typename K>
+static int grid_for(K kernel, int tpb, size_t smem, long long B) {
+  int per_sm = 0;
+  if (smem > 48 * 1024) cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, tpb, smem);
+  if (per_sm < 1) per_sm = 1;
+  int dev = 0, sms = kNumSMs;
+  cudaGetDevice(&dev);
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  long long grid = (long long)sms * per_sm;
+  if (grid > B) grid = B;
+  return (int)grid;
+}
+
+struct ModelArgs {
+  const void *p, *x, *y, *w;
+  long long ybs, ycs, B;
+  int wlen, C, N;
+  void *fA, *fB, *g, *H;
+  double *g64, *H64, *stats, *stat_out;
+  void *f_out, *J_out;
+  const nlls_ctrl* ctrl;
+  cudaStream_t st;
+};
+
+enum Op { OP_NEQ, OP_NEQ_GDA, OP_COST, OP_EVAL };
+
+template <typename T, typename Model>
+static int run_op(Op op, const ModelArgs& a) {
+  constexpr int TPB = kFusedTPB, S = kFusedS, NW = TPB / 32, P = Model::P, V = P + Tri<P>::N + 2;
+  switch (op) {
+    case OP_NEQ: {
+      const size_t smem = ((size_t)NW * V + (size_t)a.C * TPB + (size_t)a.C * NW) * 8;
+      if (smem > 200 * 1024) { set_error("fused model path: too many costs (C=%d)", a.C); return NLLS_E_SHAPE; }
+      auto kern = k_model_normal_eq<T, Model, TPB, S>;
+      const int grid = grid_for(kern, TPB, smem, a.B);
+      kern<<<grid, TPB, smem, a.st>>>((const T*)a.p, (const T*)a.x, (const T*)a.y, a.ybs, a.ycs, (const T*)a.w, a.wlen, a.B,
+                                      a.C, a.N, (T*)a.fA, (T*)a.fB, (T*)a.g, (T*)a.H, a.stats, a.ctrl);
+      return check_launch("nlls_model_normal_eq");
+    }
+    case OP_NEQ_GDA: {
+      auto kern = k_model_normal_eq_gda<T, Model, TPB>;
+      const int grid = grid_for(kern, TPB, 0, a.B);
+      kern<<<grid, TPB, 0, a.st>>>((const T*)a.p, (const T*)a.x, (const T*)a.y, a.ybs, a.ycs, (const T*)a.w, a.wlen, a.B, a.C,
+                                   a.N, (T*)a.fA, (T*)a.fB, a.g64, a.H64, a.stats, a.ctrl);
+      return check_launch("nlls_model_normal_eq_gda");
+    }
+    case OP_COST: {
+      const size_t smem = ((size_t)a.C * TPB + (size_t)a.C * NW) * 8;
+      if (smem > 200 * 1024) { set_error("fused model path: too many costs (C=%d)", a.C); return NLLS_E_SHAPE; }
+      auto kern = k_model_cost_stat<T, Model, TPB, S>;
+      const int grid = grid_for(kern, TPB, smem, a.B);
+      kern<<<grid, TPB, smem, a.st>>>((const T*)a.p, (const T*)a.x, (const T*)a.y, a.ybs, a.ycs, a.B, a.C, a.N, a.stat_out,
+                                      a.ctrl);
+      return check_launch("nlls_model_cost_stat");
+    }
+    case OP_EVAL: {
+      auto kern = k_model_eval<T, Model>;
+      long long blocks = (a.B * (long long)a.N + 255) / 256;
+      if (blocks > 148LL * 8 * 8) blocks = 148LL * 8 * 8;
+      kern<<<(int)blocks, 256, 0, a.st>>>((const T*)a.p, (const T*)a.x, (const T*)a.y, a.ybs, a.ycs, a.B, a.C, a.N,
+                                          (T*)a.f_out, (T*)a.J_out, a.ctrl);
+      return check_launch("nlls_model_eval");
+    }
+  }
+  return NLLS_E_MODEL;
+}
+
+template <typename T>
+static int run_model(int model, int P, Op op, const ModelArgs& a) {
+  if (model == NLLS_MODEL_EMG && P == 4) return run_op<T, EmgModel<T>>(op, a);
+  if (model == NLLS_MODEL_SKEWGAUSS && P == 4) return run_op<T, SkewGaussModel<T, 4>>(op, a);
+  if (model == NLLS_MODEL_SKEWGAUSS && P == 5) return run_op<T, SkewGaussModel<T, 5>>(op, a);
+  set_error("unknown model %d with P=%d (EMG: P=4, skewed Gaussian: P=4|5)", model, P);
+  return NLLS_E_MODEL;
+}
+
+static int dispatch(int model, int dtype, int P, Op op, const ModelArgs& a) {
+  if (dtype != NLLS_F32 && dtype != NLLS_F64) { set_error("dtype %d is not NLLS_F32/NLLS_F64", dtype); return NLLS_E_DTYPE; }
+  if (a.B < 0 || a.C < 1 || a.N < 1 || (op <= OP_NEQ_GDA && a.wlen != 1 && a.wlen != a.C)) {
+    set_error("unsupported shape B=%lld C=%d N=%d wlen=%d", a.B, a.C, a.N, a.wlen);
+    return NLLS_E_SHAPE;
+  }
+  if (a.B == 0) return 0;
+  if (!a.p || !a.x || !a.y) { set_error("fused model path: NULL tensor"); return NLLS_E_NULL; }
+  return dtype == NLLS_F64 ? run_model<double>(model, P, op, a) : run_model<float>(model, P, op, a);
+}
+
+}  // namespace nlls
+
+using namespace nlls;
+
+extern "C" int nlls_model_eval(int model, int dtype, const void* p, int P, const void* x, const void* y, long long y_bstride,
+                               long long y_cstride, long long B, int C, int N, void* f_out, void* J_out,
+                               const nlls_ctrl* ctrl, void* stream) {
+  ModelArgs a{};
+  a.p = p; a.x = x; a.y = y; a.ybs = y_bstride; a.ycs = y_cstride; a.B = B; a.C = C; a.N = N; a.wlen = 1;
+  a.f_out = f_out; a.J_out = J_out; a.ctrl = ctrl; a.st = (cudaStream_t)stream;
+  if (!f_out) { set_error("nlls_model_eval: NULL f_out"); return NLLS_E_NULL; }
+  return dispatch(model, dtype, P, OP_EVAL, a);
+}
+
+extern "C" int nlls_model_normal_eq(int model, int dtype, const void* p, int P, const void* x, const void* y,
+                                    long long y_bstride, long long y_cstride, const void* wvec, int wlen, long long B, int C,
+                                    int N, void* f_pp0, void* f_pp1, void* g, void* H, double* stats, const nlls_ctrl* ctrl,
+                                    void* stream) {
+  ModelArgs a{};
+  a.p = p; a.x = x; a.y = y; a.w = wvec; a.ybs = y_bstride; a.ycs = y_cstride; a.B = B; a.C = C; a.N = N; a.wlen = wlen;
+  a.fA = f_pp0; a.fB = f_pp1; a.g = g; a.H = H; a.stats = stats; a.ctrl = ctrl; a.st = (cudaStream_t)stream;
+  if (!wvec || !g || !H || !stats || (f_pp0 && !f_pp1)) { set_error("nlls_model_normal_eq: NULL tensor"); return NLLS_E_NULL; }
+  return dispatch(model, dtype, P, OP_NEQ, a);
+}
+
+extern "C" int nlls_model_normal_eq_gda(int model, int dtype, const void* p, int P, const void* x, const void* y,
+                                        long long y_bstride, long long y_cstride, const void* wvec, int wlen, long long B,
+                                        int C, int N, void* fsum_pp0, void* fsum_pp1, double* g64, double* H64, double* stats,
+                                        const nlls_ctrl* ctrl, void* stream) {
+  ModelArgs a{};
+  a.p = p; a.x = x; a.y = y; a.w = wvec; a.ybs = y_bstride; a.ycs = y_cstride; a.B = B; a.C = C; a.N = N; a.wlen = wlen;
+  a.fA = fsum_pp0; a.fB = fsum_pp1; a.g64 = g64; a.H64 = H64; a.stats = stats; a.ctrl = ctrl; a.st = (cudaStream_t)stream;
+  if (!wvec || !g64 || !H64 || !stats || (fsum_pp0 && !fsum_pp1)) { set_error("nlls_model_normal_eq_gda: NULL tensor"); return NLLS_E_NULL; }
+  return dispatch(model, dtype, P, OP_NEQ_GDA, a);
+}
+
+extern "C" int nlls_model_cost_stat(int model, int dtype, const void* p_trial, int P, const void* x, const void* y,
+                                    long long y_bstride, long long y_cstride, long long B, int C, int N, double* stat_out,
+                                    const nlls_ctrl* ctrl, void* stream) {
+  ModelArgs a{};
+  a.p = p_trial; a.x = x; a.y = y; a.ybs = y_bstride; a.ycs = y_cstride; a.B = B; a.C = C; a.N = N; a.wlen = 1;
+  a.stat_out = stat_out; a.ctrl = ctrl; a.st = (cudaStream_t)stream;
+  if (!stat_out) { set_error("nlls_model_cost_stat: NULL stat_out"); return NLLS_E_NULL; }
+  return dispatch(model, dtype, P, OP_COST, a);
+}

@@ -1,0 +1,411 @@
+// solve_update.cu — K2 (damped fp64 solve) and K3 (update, gain ratio, damping adaptation,
+// stop tests, snapshots, batch-global termination) of the batched NLLS iteration.
+//
+// One thread per problem: the P x P systems live in registers (P <= 8; Cholesky with an LU
+// fallback) or in an interleaved shared-memory scratch (8 < P <= 32).  The kernels are a few
+// microseconds at B = 65536; what they buy is the removal of the reference's ~100 small
+// launches and ~20 host synchronisations per iteration (boolean-mask indexing at
+// lma:103,105,115,131-134; `converged.all()` at lma:118) — every decision stays on the device.
+#include "common.cuh"
+
+namespace nlls {
+
+constexpr int kUpdTPB = 128;
+
+template <typename T> __device__ __forceinline__ T nan_max(T a, T b) { return (a != a) ? a : ((b != b) ? b : (a > b ? a : b)); }
+
+// ------------------------------------------------------------------- solve dispatch
+// Solves (H + diag_add*I + off_add*(1-I)) x = g in fp64.  H is TH (T or double), row-major.
+template <typename TH, typename T, int P>
+__device__ __forceinline__ bool solve_reg(const TH* __restrict__ Hb, const TH* __restrict__ gb, T diag_add, T off_add,
+                                          bool damped, double* x_out) {
+  double A[P][P], rhs[P], x[P];
+#pragma unroll
+  for (int i = 0; i < P; ++i) {
+    rhs[i] = (double)gb[i];
+#pragma unroll
+    for (int j = 0; j < P; ++j) {
+      TH v = Hb[i * P + j];
+      if (damped) v = (TH)((T)v + (i == j ? diag_add : off_add));   // Hu formed in T, then .double() (lma:97-98)
+      A[i][j] = (double)v;
+    }
+  }
+  const bool ok = spd_solve<P>(A, rhs, x);
+#pragma unroll
+  for (int i = 0; i < P; ++i) x_out[i] = x[i];
+  return ok;
+}
+
+template <typename TH, typename T>
+__device__ __forceinline__ bool solve_any(int P, const TH* Hb, const TH* gb, T diag_add, T off_add, bool damped,
+                                          double* x_out, double* scratch, int es) {
+  switch (P) {
+    case 1: return solve_reg<TH, T, 1>(Hb, gb, diag_add, off_add, damped, x_out);
+    case 2: return solve_reg<TH, T, 2>(Hb, gb, diag_add, off_add, damped, x_out);
+    case 3: return solve_reg<TH, T, 3>(Hb, gb, diag_add, off_add, damped, x_out);
+    case 4: return solve_reg<TH, T, 4>(Hb, gb, diag_add, off_add, damped, x_out);
+    case 5: return solve_reg<TH, T, 5>(Hb, gb, diag_add, off_add, damped, x_out);
+    case 6: return solve_reg<TH, T, 6>(Hb, gb, diag_add, off_add, damped, x_out);
+    case 7: return solve_reg<TH, T, 7>(Hb, gb, diag_add, off_add, damped, x_out);
+    case 8: return solve_reg<TH, T, 8>(Hb, gb, diag_add, off_add, damped, x_out);
+    default: break;
+  }
+  // runtime P: interleaved scratch, element k of this thread at scratch[k*es]
+  double* A = scratch;
+  double* W = A + (size_t)P * P * es;
+  double* b = W + (size_t)P * P * es;
+  double* x = b + (size_t)P * es;
+  for (int i = 0; i < P; ++i) {
+    b[i * es] = (double)gb[i];
+    for (int j = 0; j < P; ++j) {
+      TH v = Hb[i * P + j];
+      if (damped) v = (TH)((T)v + (i == j ? diag_add : off_add));
+      A[(i * P + j) * es] = (double)v;
+    }
+  }
+  const bool ok = spd_solve_rt(P, A, P, es, b, x, W);
+  for (int i = 0; i < P; ++i) x_out[i] = x[i * es];
+  return ok;
+}
+
+static size_t scratch_bytes_per_thread(int P) { return P > 8 ? ((size_t)2 * P * P + 2 * P) * 8 : 0; }
+static int threads_for(int P) {
+  if (P <= 8) return kUpdTPB;
+  int t = 32;
+  while (t > 1 && scratch_bytes_per_thread(P) * t > 200 * 1024) t >>= 1;
+  return t;
+}
+
+// block-wide accumulation of up to 3 per-thread 0/1 flags into ctrl->red[idx]
+__device__ __forceinline__ void block_count_add(nlls_ctrl* ctrl, int f0, int f1, int f2) {
+  __shared__ int cnt[3];
+  if (threadIdx.x < 3) cnt[threadIdx.x] = 0;
+  __syncthreads();
+  const unsigned m0 = __ballot_sync(0xffffffffu, f0), m1 = __ballot_sync(0xffffffffu, f1), m2 = __ballot_sync(0xffffffffu, f2);
+  if ((threadIdx.x & 31) == 0) {
+    if (m0) atomicAdd(&cnt[0], __popc(m0));
+    if (m1) atomicAdd(&cnt[1], __popc(m1));
+    if (m2) atomicAdd(&cnt[2], __popc(m2));
+  }
+  __syncthreads();
+  if (threadIdx.x < 3 && cnt[threadIdx.x]) atomicAdd(&ctrl->red[threadIdx.x], (double)cnt[threadIdx.x]);   // integer-valued: order-independent
+}
+
+// shared stop tests (lma:108-109, gna:78-79, gda:74-75): strict '<', NaN-propagating max (Q12)
+template <typename T>
+__device__ __forceinline__ void gp_tests(int P, const T* gb, int gstride, const T* hb, const T* pb, T gtol, T ptol,
+                                         bool& gcon, bool& pcon) {
+  T gm = fabs(gb[0]);
+  T hh = T(0), pp = T(0);
+  for (int i = 0; i < P; ++i) {
+    if (i) gm = nan_max(gm, (T)fabs(gb[i * gstride]));
+    hh = fma(hb[i], hb[i], hh);
+    pp = fma(pb[i], pb[i], pp);
+  }
+  gcon = gm < gtol;
+  pcon = sqrt(hh) < ptol * (ptol + sqrt(pp));
+}
+
+// ----------------------------------------------------------------------------- LM solve
+template <typename T>
+__global__ void k_lm_solve(const T* __restrict__ g, const T* __restrict__ H, const T* __restrict__ p,
+                           const T* __restrict__ u, T* __restrict__ dscale, int marquardt, long long B, int P,
+                           T* __restrict__ h, T* __restrict__ p_trial, nlls_ctrl* ctrl) {
+  if (is_done(ctrl)) return;
+  extern __shared__ double scratch[];
+  const long long b = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (b >= B) return;
+  const T* Hb = H + b * P * P;
+  T dd = dscale[b * 2], doff = dscale[b * 2 + 1];
+  if (marquardt) {                                   // lma:88 — D <- D * max_p max(H_pp, D_pp)   (Q6)
+    T m = nan_max(Hb[0], dd);
+    for (int i = 1; i < P; ++i) m = nan_max(m, nan_max(Hb[i * P + i], dd));
+    dd = dd * m;
+    doff = doff * m;                                 // 0 * inf -> NaN exactly like the reference's dense D
+    dscale[b * 2] = dd;
+    dscale[b * 2 + 1] = doff;
+  }
+  const T ub = u[b];
+  double x[NLLS_MAX_P];
+  const bool ok = solve_any<T, T>(P, Hb, g + b * P, ub * dd, ub * doff, true, x, scratch + threadIdx.x, blockDim.x);
+  if (!ok && ctrl) ctrl->singular = 1;
+  for (int i = 0; i < P; ++i) {
+    const T hi = -(T)x[i];                           // lma:98
+    h[b * P + i] = hi;
+    p_trial[b * P + i] = p[b * P + i] + hi;          // argument of the trial cost (lma:99)
+  }
+}
+
+// ---------------------------------------------------------------------------- LM update
+template <typename T>
+__global__ void k_lm_update(T* __restrict__ p, const T* __restrict__ h, const T* __restrict__ g, T* __restrict__ u,
+                            T* __restrict__ v, const double* __restrict__ stats, const double* __restrict__ stat_h,
+                            int meth, T rho1, T rho2, T beta, T gama, double ftol, T ptol, T gtol, long long B, int P,
+                            T* __restrict__ p_hist, T* __restrict__ rho_out, nlls_ctrl* ctrl) {
+  if (is_done(ctrl)) return;
+  const int it = iter_index(ctrl);
+  const long long b = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  int nc_open = 0, accepted = 0, nc_closed = 0;
+  if (b < B) {
+    const T* hb = h + b * P;
+    const T* gb = g + b * P;
+    T* pb = p + b * P;
+    T ub = u[b], vb = v[b];
+    // gain ratio (lma:100-103); the numerator is sum_c (sum_n f)^2 differences (Q3)
+    const T num = (T)stats[b * 4 + 0] - (T)stat_h[b];
+    T den = T(0);
+    for (int i = 0; i < P; ++i) den = fma(hb[i], ub * hb[i] - gb[i], den);
+    T rho = num / den;
+    const T INF = (T)__longlong_as_double(0x7ff0000000000000LL);
+    if (den == T(0)) rho = (num > T(0)) ? INF : -INF;
+    if (rho_out) rho_out[b] = rho;
+    if (meth == NLLS_LM_LEVENBERG) {                 // lma:124-136 (Q9): NaN / zero rho changes nothing
+      if (rho > T(0)) {
+        const T t = T(2) * rho - T(1);
+        const T fac = T(1) - t * t * t;
+        const T third = T(1) / T(3);
+        ub *= (fac > third || fac != fac) ? fac : third;
+        vb = T(2);
+      } else if (rho < T(0)) {
+        ub *= vb;
+        vb *= T(2);
+      }
+    } else {                                         // lma:139-152
+      if (rho < rho1) ub *= beta;
+      if (rho > rho2) ub /= gama;
+    }
+    u[b] = ub;
+    v[b] = vb;
+    accepted = rho > T(0);
+    if (accepted)
+      for (int i = 0; i < P; ++i) pb[i] += hb[i];    // lma:105, in place on the caller's p (Q1)
+    bool gcon, pcon;
+    gp_tests<T>(P, gb, 1, hb, pb, gtol, ptol, gcon, pcon);   // p already updated (Q2)
+    const bool fcon = (it > 0) && (stats[b * 4 + 1] < ftol * ftol * stats[b * 4 + 2]);   // lma:110
+    nc_open = !(gcon || pcon || fcon);
+    nc_closed = !(gcon || pcon);
+    if (p_hist) {
+      T* snap = p_hist + ((long long)it * B + b) * P;
+      for (int i = 0; i < P; ++i) snap[i] = pb[i];   // lma:116
+    }
+  }
+  if (ctrl) block_count_add(ctrl, nc_open, accepted, nc_closed);
+}
+
+// ---------------------------------------------------------------------------- GN update
+template <typename T>
+__global__ void k_gn_update(T* __restrict__ p, const T* __restrict__ g, const T* __restrict__ H,
+                            const double* __restrict__ stats, T l, double ftol, T ptol, T gtol, int with_masks,
+                            long long B, int P, T* __restrict__ h_out, T* __restrict__ p_hist, nlls_ctrl* ctrl) {
+  if (is_done(ctrl)) return;
+  extern __shared__ double scratch[];
+  const int it = iter_index(ctrl);
+  const long long b = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  int nc = 0;
+  if (b < B) {
+    double x[NLLS_MAX_P];
+    const bool ok = solve_any<T, T>(P, H + b * P * P, g + b * P, T(0), T(0), false, x, scratch + threadIdx.x, blockDim.x);
+    if (!ok && ctrl) ctrl->singular = 1;             // gna:74-75 warns on an infinite condition number
+    T hb[NLLS_MAX_P];
+    T* pb = p + b * P;
+    for (int i = 0; i < P; ++i) {
+      hb[i] = (T)x[i];                               // gna:140
+      pb[i] -= l * hb[i];                            // gna:141 (in place, Q1)
+      if (h_out) h_out[b * P + i] = hb[i];
+    }
+    if (with_masks) {
+      bool gcon, pcon;
+      gp_tests<T>(P, g + b * P, 1, hb, pb, gtol, ptol, gcon, pcon);
+      const bool fcon = (it > 0) && (stats[b * 4 + 1] < ftol * ftol * stats[b * 4 + 2]);   // gna:80
+      nc = !(gcon || pcon || fcon);
+    }
+    if (p_hist) {
+      T* snap = p_hist + ((long long)it * B + b) * P;
+      for (int i = 0; i < P; ++i) snap[i] = pb[i];   // gna:86
+    }
+  }
+  if (ctrl && with_masks) block_count_add(ctrl, nc, 0, 0);
+}
+
+// ---------------------------------------------------------------------------- GD update
+template <typename T>
+__global__ void k_gd_update(T* __restrict__ p, const double* __restrict__ g64, const double* __restrict__ H64, T l,
+                            T ptol, T gtol, int with_masks, long long B, int P, T* __restrict__ h_out,
+                            T* __restrict__ p_hist, nlls_ctrl* ctrl) {
+  if (is_done(ctrl)) return;
+  extern __shared__ double scratch[];
+  const int it = iter_index(ctrl);
+  const long long b = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  int nc = 0;
+  if (b < B) {
+    double x[NLLS_MAX_P];
+    const bool ok = solve_any<double, double>(P, H64 + b * P * P, g64 + b * P, 0.0, 0.0, false, x, scratch + threadIdx.x, blockDim.x);
+    if (!ok && ctrl) ctrl->singular = 1;
+    T hb[NLLS_MAX_P], gb[NLLS_MAX_P];
+    T* pb = p + b * P;
+    for (int i = 0; i < P; ++i) {
+      hb[i] = (T)x[i];                               // gda:139
+      pb[i] -= l * hb[i];                            // gda:146
+      gb[i] = hb[i] / l;                             // gda:71
+      if (h_out) h_out[b * P + i] = hb[i];
+    }
+    if (with_masks) {
+      bool gcon, pcon;
+      gp_tests<T>(P, gb, 1, hb, pb, gtol, ptol, gcon, pcon);
+      nc = !(gcon || pcon);
+    }
+    if (p_hist) {
+      T* snap = p_hist + ((long long)it * B + b) * P;
+      for (int i = 0; i < P; ++i) snap[i] = pb[i];
+    }
+  }
+  if (ctrl && with_masks) block_count_add(ctrl, nc, 0, 0);
+}
+
+// Deterministic batch-global sums of stats[:,1] and stats[:,2] into red[2], red[3] (gda:76, Q5):
+// one CTA, fixed per-thread strides, fixed tree.
+__global__ void __launch_bounds__(1024) k_reduce_stats(const double* __restrict__ stats, long long B, nlls_ctrl* ctrl) {
+  if (is_done(ctrl)) return;
+  __shared__ double s1[1024], s2[1024];
+  double a = 0.0, c = 0.0;
+  for (long long b = threadIdx.x; b < B; b += 1024) { a += stats[b * 4 + 1]; c += stats[b * 4 + 2]; }
+  s1[threadIdx.x] = a;
+  s2[threadIdx.x] = c;
+  __syncthreads();
+  for (int s = 512; s > 0; s >>= 1) {
+    if (threadIdx.x < s) { s1[threadIdx.x] += s1[threadIdx.x + s]; s2[threadIdx.x] += s2[threadIdx.x + s]; }
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) { ctrl->red[2] += s1[0]; ctrl->red[3] += s2[0]; }
+}
+
+__global__ void k_iter_end(nlls_ctrl* ctrl, int solver, double ftol) {
+  if (ctrl->done) return;
+  const int it = ctrl->iters;
+  bool done;
+  if (solver == NLLS_SOLVER_LM) {
+    const bool gate = ctrl->red[1] > 0.0;            // (rho > 0).sum() > 0  (lma:110, Q10)
+    done = (gate ? ctrl->red[0] : ctrl->red[2]) == 0.0;
+  } else if (solver == NLLS_SOLVER_GD) {
+    const bool fcon = (it > 0) && (ctrl->red[2] < ftol * ftol * ctrl->red[3]);   // batch-global (Q5)
+    done = fcon || ctrl->red[0] == 0.0;
+  } else {
+    done = ctrl->red[0] == 0.0;
+  }
+  ctrl->iters = it + 1;
+  ctrl->done = done ? 1 : 0;
+  ctrl->red[0] = ctrl->red[1] = ctrl->red[2] = ctrl->red[3] = 0.0;
+}
+
+template <typename K>
+static void allow_smem(K kern, size_t smem) {
+  if (smem > 48 * 1024) cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+}
+
+}  // namespace nlls
+
+using namespace nlls;
+
+static int check_bp(int dtype, long long B, int P) {
+  if (dtype != NLLS_F32 && dtype != NLLS_F64) { set_error("dtype %d is not NLLS_F32/NLLS_F64", dtype); return NLLS_E_DTYPE; }
+  if (B < 0 || P < 1 || P > NLLS_MAX_P) { set_error("unsupported shape B=%lld P=%d", B, P); return NLLS_E_SHAPE; }
+  return 0;
+}
+
+extern "C" int nlls_lm_solve(int dtype, const void* g, const void* H, const void* p, const void* u, void* dscale,
+                             int marquardt, long long B, int P, void* h, void* p_trial, nlls_ctrl* ctrl, void* stream) {
+  if (int e = check_bp(dtype, B, P)) return e;
+  if (B == 0) return 0;
+  if (!g || !H || !p || !u || !dscale || !h || !p_trial) { set_error("nlls_lm_solve: NULL tensor"); return NLLS_E_NULL; }
+  const int tpb = threads_for(P);
+  const size_t smem = scratch_bytes_per_thread(P) * tpb;
+  const int grid = (int)((B + tpb - 1) / tpb);
+  cudaStream_t st = (cudaStream_t)stream;
+  if (dtype == NLLS_F64) {
+    allow_smem(k_lm_solve<double>, smem);
+    k_lm_solve<double><<<grid, tpb, smem, st>>>((const double*)g, (const double*)H, (const double*)p, (const double*)u,
+                                                (double*)dscale, marquardt, B, P, (double*)h, (double*)p_trial, ctrl);
+  } else {
+    allow_smem(k_lm_solve<float>, smem);
+    k_lm_solve<float><<<grid, tpb, smem, st>>>((const float*)g, (const float*)H, (const float*)p, (const float*)u,
+                                               (float*)dscale, marquardt, B, P, (float*)h, (float*)p_trial, ctrl);
+  }
+  return check_launch("nlls_lm_solve");
+}
+
+extern "C" int nlls_lm_update(int dtype, void* p, const void* h, const void* g, void* u, void* v, const double* stats,
+                              const double* stat_h, int meth, double rho1, double rho2, double beta, double gama,
+                              double ftol, double ptol, double gtol, long long B, int P, void* p_hist, void* rho_out,
+                              nlls_ctrl* ctrl, void* stream) {
+  if (int e = check_bp(dtype, B, P)) return e;
+  if (B == 0) return 0;
+  if (!p || !h || !g || !u || !v || !stats || !stat_h) { set_error("nlls_lm_update: NULL tensor"); return NLLS_E_NULL; }
+  const int grid = (int)((B + kUpdTPB - 1) / kUpdTPB);
+  cudaStream_t st = (cudaStream_t)stream;
+  if (dtype == NLLS_F64)
+    k_lm_update<double><<<grid, kUpdTPB, 0, st>>>((double*)p, (const double*)h, (const double*)g, (double*)u, (double*)v,
+                                                  stats, stat_h, meth, rho1, rho2, beta, gama, ftol, ptol, gtol, B, P,
+                                                  (double*)p_hist, (double*)rho_out, ctrl);
+  else
+    k_lm_update<float><<<grid, kUpdTPB, 0, st>>>((float*)p, (const float*)h, (const float*)g, (float*)u, (float*)v, stats,
+                                                 stat_h, meth, (float)rho1, (float)rho2, (float)beta, (float)gama, ftol,
+                                                 (float)ptol, (float)gtol, B, P, (float*)p_hist, (float*)rho_out, ctrl);
+  return check_launch("nlls_lm_update");
+}
+
+extern "C" int nlls_gn_update(int dtype, void* p, const void* g, const void* H, const double* stats, double l, double ftol,
+                              double ptol, double gtol, int with_masks, long long B, int P, void* h_out, void* p_hist,
+                              nlls_ctrl* ctrl, void* stream) {
+  if (int e = check_bp(dtype, B, P)) return e;
+  if (B == 0) return 0;
+  if (!p || !g || !H || (with_masks && !stats)) { set_error("nlls_gn_update: NULL tensor"); return NLLS_E_NULL; }
+  const int tpb = threads_for(P);
+  const size_t smem = scratch_bytes_per_thread(P) * tpb;
+  const int grid = (int)((B + tpb - 1) / tpb);
+  cudaStream_t st = (cudaStream_t)stream;
+  if (dtype == NLLS_F64) {
+    allow_smem(k_gn_update<double>, smem);
+    k_gn_update<double><<<grid, tpb, smem, st>>>((double*)p, (const double*)g, (const double*)H, stats, l, ftol, ptol, gtol,
+                                                 with_masks, B, P, (double*)h_out, (double*)p_hist, ctrl);
+  } else {
+    allow_smem(k_gn_update<float>, smem);
+    k_gn_update<float><<<grid, tpb, smem, st>>>((float*)p, (const float*)g, (const float*)H, stats, (float)l, ftol,
+                                                (float)ptol, (float)gtol, with_masks, B, P, (float*)h_out, (float*)p_hist,
+                                                ctrl);
+  }
+  return check_launch("nlls_gn_update");
+}
+
+extern "C" int nlls_gd_update(int dtype, void* p, const double* g64, const double* H64, const double* stats, double l,
+                              double ftol, double ptol, double gtol, int with_masks, long long B, int P, void* h_out,
+                              void* p_hist, nlls_ctrl* ctrl, void* stream) {
+  (void)ftol;
+  if (int e = check_bp(dtype, B, P)) return e;
+  if (B == 0) return 0;
+  if (!p || !g64 || !H64 || (with_masks && (!stats || !ctrl))) { set_error("nlls_gd_update: NULL tensor"); return NLLS_E_NULL; }
+  const int tpb = threads_for(P);
+  const size_t smem = scratch_bytes_per_thread(P) * tpb;
+  const int grid = (int)((B + tpb - 1) / tpb);
+  cudaStream_t st = (cudaStream_t)stream;
+  if (dtype == NLLS_F64) {
+    allow_smem(k_gd_update<double>, smem);
+    k_gd_update<double><<<grid, tpb, smem, st>>>((double*)p, g64, H64, l, ptol, gtol, with_masks, B, P, (double*)h_out,
+                                                 (double*)p_hist, ctrl);
+  } else {
+    allow_smem(k_gd_update<float>, smem);
+    k_gd_update<float><<<grid, tpb, smem, st>>>((float*)p, g64, H64, (float)l, (float)ptol, (float)gtol, with_masks, B, P,
+                                                (float*)h_out, (float*)p_hist, ctrl);
+  }
+  if (int e = check_launch("nlls_gd_update")) return e;
+  if (with_masks) {
+    k_reduce_stats<<<1, 1024, 0, st>>>(stats, B, ctrl);
+    return check_launch("nlls_gd_update(reduce)");
+  }
+  return 0;
+}
+
+extern "C" int nlls_iter_end(nlls_ctrl* ctrl, int solver, double ftol, void* stream) {
+  if (!ctrl) { set_error("nlls_iter_end: NULL ctrl"); return NLLS_E_NULL; }
+  k_iter_end<<<1, 1, 0, (cudaStream_t)stream>>>(ctrl, solver, ftol);
+  return check_launch("nlls_iter_end");
+}

@@ -1,0 +1,268 @@
+"""Host driver shared by the three batched solvers.
+
+It owns the work buffers and the device-resident control block and enqueues, per iteration, the
+C-ABI kernels of include/nlls_b200.h.  Two ways to produce the normal equations:
+
+  tensor path  opaque Python callables materialise f [B,C,N] and J [B,C,N,P]; K1
+               (nlls_normal_eq / nlls_normal_eq_gda) streams them once.  One 12-byte flag read
+               per iteration tells the host when the batch is done (the reference syncs ~20x).
+  fused path   both callables belong to a built-in FusedModel: nlls_model_normal_eq* evaluates
+               the model in-kernel.  Iterations are enqueued ahead in groups; every kernel
+               returns at once when ctrl->done is set, so the host never waits inside a group.
+
+Semantics mirror the reference exactly: in-place mutation of the caller's p,
+no freezing of converged problems, batch-global termination, per-iteration snapshots.
+"""
+import warnings
+
+import torch
+
+from ... import _lib
+from ...models import fused_model_of
+from ..jacobian import batch_jacobian_approx_t
+
+GN, LM, GD = _lib.SOLVER_GN, _lib.SOLVER_LM, _lib.SOLVER_GD
+_HIST_CHUNK_BYTES = 256 << 20
+_GROUP = 4                      # fused path: iterations enqueued between flag reads
+
+
+_default_reduce_hook = None
+
+
+def set_default_reduce_hook(hook):
+    """Installs the multi-GPU 'exact' reduction hook used by solve(); returns the previous one."""
+    global _default_reduce_hook
+    old, _default_reduce_hook = _default_reduce_hook, hook
+    return old
+
+
+def bind_callables(function, jac_function, args):
+    """reference: lma_fun_parallel.py:62-72 (identical in gna:53-63, gda:51-61)."""
+    fun = (lambda q: function(q, *args)) if len(args) > 0 else function
+    if jac_function is None:
+        jac = lambda q: batch_jacobian_approx_t(q, f=fun)
+    else:
+        jac = lambda q: jac_function(q, *args)
+    return fun, jac
+
+
+def _as_work(t, dtype, what, shape=None):
+    if not torch.is_tensor(t):
+        raise _lib.NllsError(f'{what} must return a tensor, got {type(t).__name__}')
+    _lib.require_cuda(t)
+    if shape is not None and tuple(t.shape) != tuple(shape):
+        raise _lib.NllsError(f'{what} returned shape {tuple(t.shape)}, expected {tuple(shape)}')
+    if t.dtype != dtype:
+        t = t.to(dtype)
+    return t.detach().contiguous()
+
+
+class Workspace:
+    """Per-solve device buffers (allocated once; nothing is allocated inside the loop)."""
+
+    def __init__(self, p, wvec, solver):
+        _lib.require_cuda(p)
+        self.dtype, self.device = p.dtype, p.device
+        self.code = _lib.dtype_code(p)
+        self.B, self.P = p.shape
+        if not 1 <= self.P <= 32:
+            raise _lib.NllsError(f'P={self.P} unsupported (1 <= P <= 32)')
+        B, P, kw = self.B, self.P, dict(dtype=p.dtype, device=p.device)
+        k64 = dict(dtype=torch.float64, device=p.device)
+        self.solver = solver
+        self.w = (torch.ones(1, **kw) if wvec is None else wvec.to(**kw)).contiguous()
+        self.ctrl = torch.zeros(_lib.CTRL_BYTES // 8, **k64)
+        self.ctrl_i32 = self.ctrl.view(torch.int32)
+        self.stats = torch.zeros(B, 4, **k64)
+        if solver == GD:
+            self.g = torch.empty(B, P, **k64)
+            self.H = torch.empty(B, P, P, **k64)
+        else:
+            self.g = torch.empty(B, P, **kw)
+            self.H = torch.empty(B, P, P, **kw)
+        if solver == LM:
+            self.h = torch.empty(B, P, **kw)
+            self.p_trial = torch.empty(B, P, **kw)
+            self.stat_h = torch.empty(B, **k64)
+            self.u = torch.empty(B, **kw)
+            self.v = torch.empty(B, **kw)
+            self.dscale = torch.empty(B, 2, **kw)
+        self.hist = []                 # (first_iteration, tensor[chunk,B,P])
+        self.hist_chunk = max(1, _HIST_CHUNK_BYTES // max(1, B * P * p.element_size()))
+
+    # snapshots ------------------------------------------------------------------------------
+    def hist_base_ptr(self, k, max_iter):
+        """Device address such that snapshot k lands at base + k*B*P*s; grows the history in
+        chunks so max_iter=10^4 does not allocate 10^4 snapshots up front."""
+        if not self.hist or k >= self.hist[-1][0] + self.hist[-1][1].shape[0]:
+            n = min(self.hist_chunk, max_iter - k)
+            self.hist.append((k, torch.empty(n, self.B, self.P, dtype=self.dtype, device=self.device)))
+        k0, buf = self.hist[-1]
+        return buf.data_ptr() - k0 * self.B * self.P * buf.element_size()
+
+    def hist_room(self, k):
+        k0, buf = self.hist[-1]
+        return k0 + buf.shape[0] - k
+
+    def snapshots(self, iters):
+        out = []
+        for k0, buf in self.hist:
+            n = min(buf.shape[0], iters - k0)
+            if n <= 0:
+                break
+            part = buf[:n]
+            if n * 2 < buf.shape[0]:
+                part = part.clone()
+            out.extend(part.unbind(0))
+        return out
+
+    def flags(self):
+        """(done, iters, singular) — one small device->host read."""
+        d, it, sing = self.ctrl_i32[:3].tolist()
+        return d, it, sing
+
+
+def _check_p(p):
+    assert len(p.shape) == 2, 'parameter tensor is supposed to have 2 dims, but has %s' % str(len(p.shape))
+    _lib.require_cuda(p)
+    _lib.dtype_code(p)
+
+
+def solve(solver, p, function, jac_function, args, wvec, ftol, ptol, gtol, max_iter, l=1.,
+          lm=None, fused=True, check_every=_GROUP, reduce_hook=None):
+    """Runs one batched solve; returns the list of per-iteration snapshots (coeffs_list).
+    reduce_hook(red) — optional, multi-GPU 'exact' mode: called between the update kernel and
+    nlls_iter_end with the 4 fp64 batch-global sums of the control block (a device tensor view)
+    so that a caller can all-reduce(SUM) them over the ranks (torchimize_b200/sharding.py)."""
+    _check_p(p)
+    if p.shape[0] == 0 or max_iter <= 0:
+        return []
+    if reduce_hook is None:
+        reduce_hook = _default_reduce_hook
+    work_p = p if p.is_contiguous() else p.contiguous()
+    ws = Workspace(work_p, wvec, solver)
+    model = fused_model_of(function, jac_function) if fused else None
+    st = _lib.stream_ptr
+    B, P, code = ws.B, ws.P, ws.code
+    ctrl = _lib.ptr(ws.ctrl)
+    if solver == LM:
+        ws.u.fill_(lm['tau'])                    # u = tau * max diag(I)   (lma:77-78, Q8)
+        ws.v.fill_(2.)
+        ws.dscale[:, 0] = 1.
+        ws.dscale[:, 1] = 0.
+        meth = _lib.LM_LEVENBERG if lm['meth'] == 'lev' else _lib.LM_MARQUARDT
+
+    def update(k_hist_ptr):
+        if solver == GN:
+            _lib.call('nlls_gn_update', code, _lib.ptr(work_p), _lib.ptr(ws.g), _lib.ptr(ws.H), _lib.ptr(ws.stats),
+                      float(l), ftol, ptol, gtol, 1, B, P, None, k_hist_ptr, ctrl, st())
+        elif solver == GD:
+            _lib.call('nlls_gd_update', code, _lib.ptr(work_p), _lib.ptr(ws.g), _lib.ptr(ws.H), _lib.ptr(ws.stats),
+                      float(l), ftol, ptol, gtol, 1, B, P, None, k_hist_ptr, ctrl, st())
+        else:
+            _lib.call('nlls_lm_update', code, _lib.ptr(work_p), _lib.ptr(ws.h), _lib.ptr(ws.g), _lib.ptr(ws.u),
+                      _lib.ptr(ws.v), _lib.ptr(ws.stats), _lib.ptr(ws.stat_h), meth, float(lm['rho1']), float(lm['rho2']),
+                      float(lm['beta']), float(lm['gama']), ftol, ptol, gtol, B, P, k_hist_ptr, None, ctrl, st())
+        if reduce_hook is not None:
+            reduce_hook(ws.ctrl[2:6])
+        _lib.call('nlls_iter_end', ctrl, solver, ftol, st())
+
+    def lm_solve():
+        _lib.call('nlls_lm_solve', code, _lib.ptr(ws.g), _lib.ptr(ws.H), _lib.ptr(work_p), _lib.ptr(ws.u),
+                  _lib.ptr(ws.dscale), int(meth == _lib.LM_MARQUARDT), B, P, _lib.ptr(ws.h), _lib.ptr(ws.p_trial), ctrl, st())
+
+    if model is not None:
+        # ------------------------------------------------------------------ fused path
+        x, y, ybs, ycs, C, N = model.layout(work_p, *args)
+        if ws.w.numel() not in (1, C):
+            raise _lib.NllsError(f'wvec has {ws.w.numel()} entries for {C} costs')
+        mid = model.model_id
+        if solver == GD:
+            fpp = torch.empty(2, B, N, dtype=ws.dtype, device=ws.device)
+        else:
+            fpp = torch.empty(2, B, C, N, dtype=ws.dtype, device=ws.device)
+        launched, done = 0, False
+        while launched < max_iter and not done:
+            hp = ws.hist_base_ptr(launched, max_iter)
+            group = min(check_every, max_iter - launched, ws.hist_room(launched))
+            for _ in range(group):
+                if solver == GD:
+                    _lib.call('nlls_model_normal_eq_gda', mid, code, _lib.ptr(work_p), P, _lib.ptr(x), _lib.ptr(y), ybs, ycs,
+                              _lib.ptr(ws.w), ws.w.numel(), B, C, N, _lib.ptr(fpp[0]), _lib.ptr(fpp[1]), _lib.ptr(ws.g),
+                              _lib.ptr(ws.H), _lib.ptr(ws.stats), ctrl, st())
+                else:
+                    _lib.call('nlls_model_normal_eq', mid, code, _lib.ptr(work_p), P, _lib.ptr(x), _lib.ptr(y), ybs, ycs,
+                              _lib.ptr(ws.w), ws.w.numel(), B, C, N, _lib.ptr(fpp[0]), _lib.ptr(fpp[1]), _lib.ptr(ws.g),
+                              _lib.ptr(ws.H), _lib.ptr(ws.stats), ctrl, st())
+                if solver == LM:
+                    lm_solve()
+                    _lib.call('nlls_model_cost_stat', mid, code, _lib.ptr(ws.p_trial), P, _lib.ptr(x), _lib.ptr(y), ybs, ycs,
+                              B, C, N, _lib.ptr(ws.stat_h), ctrl, st())
+                update(hp)
+            launched += group
+            done, iters, sing = ws.flags()
+        done, iters, sing = ws.flags()
+    else:
+        # ----------------------------------------------------------------- tensor path
+        fun, jac = bind_callables(function, jac_function, args)
+        f_prev = None
+        iters, sing = 0, 0
+        for k in range(max_iter):
+            f = _as_work(fun(work_p), ws.dtype, 'function')
+            if f.dim() != 3 or f.shape[0] != B:
+                raise _lib.NllsError(f'function must return [B,C,N] residuals, got {tuple(f.shape)}')
+            _, C, N = f.shape
+            J = _as_work(jac(work_p), ws.dtype, 'jac_function', (B, C, N, P))
+            if ws.w.numel() not in (1, C):
+                raise _lib.NllsError(f'wvec has {ws.w.numel()} entries for {C} costs')
+            hp = ws.hist_base_ptr(k, max_iter)
+            if solver == GD:
+                fs = torch.empty(B, N, dtype=ws.dtype, device=ws.device)
+                _lib.call('nlls_normal_eq_gda', code, _lib.ptr(J), _lib.ptr(f), _lib.ptr(f_prev), _lib.ptr(ws.w),
+                          ws.w.numel(), B, C, N, P, _lib.ptr(ws.g), _lib.ptr(ws.H), _lib.ptr(fs), _lib.ptr(ws.stats), ctrl, st())
+                keep = fs
+            else:
+                _lib.call('nlls_normal_eq', code, _lib.ptr(J), _lib.ptr(f), _lib.ptr(f_prev), _lib.ptr(ws.w), ws.w.numel(),
+                          B, C, N, P, _lib.ptr(ws.g), _lib.ptr(ws.H), _lib.ptr(ws.stats), ctrl, st())
+                keep = f
+            if solver == LM:
+                lm_solve()
+                f_h = _as_work(fun(ws.p_trial), ws.dtype, 'function', (B, C, N))       # lma:99
+                _lib.call('nlls_cost_stat', code, _lib.ptr(f_h), B, C, N, _lib.ptr(ws.stat_h), ctrl, st())
+            update(hp)
+            f_prev = keep                                   # pointer swap instead of f.clone() (lma:111)
+            done, iters, sing = ws.flags()
+            if done:
+                break
+    if sing and solver == GN:
+        # reference: gna_fun_parallel.py:74-75 (there: cond(H) is inf, via a batched SVD every iteration)
+        warnings.warn('Condition number of at least one Hessian is infinite giving NaNs. Consider a step rate l<1.')
+    if work_p is not p:
+        p.copy_(work_p)                                     # Q1: the caller's tensor ends as the final iterate
+    return ws.snapshots(iters)
+
+
+def plain(solver, p, function, jac_function, wvec, l, max_iter):
+    """Fixed-iteration variants (gna:94-117, gda:90-113): no stop tests, returns the final p."""
+    _check_p(p)
+    work_p = p if p.is_contiguous() else p.contiguous()
+    ws = Workspace(work_p, wvec, solver)
+    B, P, code = ws.B, ws.P, ws.code
+    st = _lib.stream_ptr
+    for _ in range(max_iter):
+        f = _as_work(function(work_p), ws.dtype, 'function')
+        _, C, N = f.shape
+        J = _as_work(jac_function(work_p), ws.dtype, 'jac_function', (B, C, N, P))
+        if solver == GD:
+            _lib.call('nlls_normal_eq_gda', code, _lib.ptr(J), _lib.ptr(f), None, _lib.ptr(ws.w), ws.w.numel(), B, C, N, P,
+                      _lib.ptr(ws.g), _lib.ptr(ws.H), None, _lib.ptr(ws.stats), None, st())
+            _lib.call('nlls_gd_update', code, _lib.ptr(work_p), _lib.ptr(ws.g), _lib.ptr(ws.H), None, float(l), 0., 0., 0., 0,
+                      B, P, None, None, None, st())
+        else:
+            _lib.call('nlls_normal_eq', code, _lib.ptr(J), _lib.ptr(f), None, _lib.ptr(ws.w), ws.w.numel(), B, C, N, P,
+                      _lib.ptr(ws.g), _lib.ptr(ws.H), _lib.ptr(ws.stats), None, st())
+            _lib.call('nlls_gn_update', code, _lib.ptr(work_p), _lib.ptr(ws.g), _lib.ptr(ws.H), None, float(l), 0., 0., 0., 0,
+                      B, P, None, None, None, st())
+    if work_p is not p:
+        p.copy_(work_p)
+    return p

@@ -1,0 +1,95 @@
+"""Built-in fit models with fused CUDA residual+Jacobian kernels (K4).
+
+A model object supplies the two callables the reference's solvers expect —
+``function(p, x, y) -> [B,C,N]`` and ``jac_function(p, x, y) -> [B,C,N,P]``
+(README.rst:97-98) — backed by ``nlls_model_eval``.  When BOTH callables handed to a solver are
+the bound ``cost`` / ``jac`` methods of the same model object, the solver skips materialising
+J altogether and runs the fused normal-equation kernels instead (``nlls_model_normal_eq*``).
+
+    emg = EMGModel(n_costs=2)
+    coeffs = lsq_lma_parallel(p, emg.cost, emg.jac, args=(t, y), wvec=torch.ones(2, ...))
+
+Models (definitions follow the reference's tests):
+  EMGModel            p=[alpha, mu, sigma, eta]   tests/emg.py:19-49, tests/unit_test_parallel.py:81-118
+  SkewGaussModel      p=[norm, mean, sigm, skew(, offset)]   tests/unit_test_skewed_gaussian.py:43-51
+Cost is the squared error (y - m)^2 used as residual, as in tests/unit_test_parallel.py:40,55-56.
+"""
+import torch
+
+from . import _lib
+
+
+class FusedModel:
+    """Base: data layout handling shared by all built-in models."""
+    model_id = -1
+    n_params = ()
+
+    def __init__(self, n_costs=None):
+        # n_costs: number of cost channels when y is [B,N] (one data row shared by all costs, as in
+        # the reference's multi_cost_batch); ignored when y is [B,C,N].
+        self.n_costs = n_costs
+
+    # -- layout -----------------------------------------------------------------------------
+    def layout(self, p, x, y):
+        """-> (x, y, y_bstride, y_cstride, C, N) with x, y contiguous in p's dtype on p's device."""
+        _lib.require_cuda(p, x, y)
+        if p.dim() != 2 or p.shape[1] not in self.n_params:
+            raise _lib.NllsError(f'{type(self).__name__}: p must be [B,P] with P in {self.n_params}, got {tuple(p.shape)}')
+        x = x.to(dtype=p.dtype).contiguous()
+        y = y.to(dtype=p.dtype).contiguous()
+        N = x.shape[0]
+        if y.dim() == 2:
+            C = 1 if self.n_costs is None else int(self.n_costs)
+            ybs, ycs = N, 0
+        elif y.dim() == 3:
+            C = y.shape[1]
+            ybs, ycs = C * N, N
+        else:
+            raise _lib.NllsError(f'y must be [B,N] or [B,C,N], got {tuple(y.shape)}')
+        if y.shape[0] != p.shape[0] or y.shape[-1] != N or x.dim() != 1:
+            raise _lib.NllsError(f'shape mismatch: p {tuple(p.shape)}, x {tuple(x.shape)}, y {tuple(y.shape)}')
+        return x, y, ybs, ycs, C, N
+
+    # -- the reference-style callables ------------------------------------------------------
+    def _eval(self, p, x, y, want_jac):
+        x, y, ybs, ycs, C, N = self.layout(p, x, y)
+        pc = p.contiguous()
+        B, P = pc.shape
+        f = torch.empty((B, C, N), dtype=p.dtype, device=p.device)
+        J = torch.empty((B, C, N, P), dtype=p.dtype, device=p.device) if want_jac else None
+        _lib.call('nlls_model_eval', self.model_id, _lib.dtype_code(p), _lib.ptr(pc), P, _lib.ptr(x), _lib.ptr(y),
+                  ybs, ycs, B, C, N, _lib.ptr(f), _lib.ptr(J), None, _lib.stream_ptr())
+        return f, J
+
+    def cost(self, p, x, y):
+        """function(p, x, y) -> residuals [B,C,N] = (y - m)^2."""
+        return self._eval(p, x, y, False)[0]
+
+    def jac(self, p, x, y):
+        """jac_function(p, x, y) -> Jacobian [B,C,N,P] of ``cost``."""
+        return self._eval(p, x, y, True)[1]
+
+    def cost_and_jac(self, p, x, y):
+        return self._eval(p, x, y, True)
+
+
+class EMGModel(FusedModel):
+    model_id = _lib.MODEL_EMG
+    n_params = (4,)
+
+
+class SkewGaussModel(FusedModel):
+    model_id = _lib.MODEL_SKEWGAUSS
+    n_params = (4, 5)
+
+
+def fused_model_of(function, jac_function):
+    """The FusedModel both callables belong to, else None (=> tensor path)."""
+    owner = getattr(function, '__self__', None)
+    if not isinstance(owner, FusedModel) or getattr(function, '__func__', None) is not FusedModel.cost:
+        return None
+    if jac_function is None:
+        return owner          # analytic Jacobian of the built-in model stands in for autograd's
+    if getattr(jac_function, '__self__', None) is owner and getattr(jac_function, '__func__', None) is FusedModel.jac:
+        return owner
+    return None

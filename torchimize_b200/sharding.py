@@ -1,0 +1,80 @@
+"""Multi-GPU sharding of the batch dimension.
+
+Problems are independent, so B is split into contiguous shards, one process per GPU
+(torch.distributed, NCCL over NVLink/NVSwitch).  The data path has NO per-iteration collective:
+
+  mode='local'  each rank iterates until ITS shard is done; one all-gather of the finals.
+  mode='exact'  additionally all-reduces the 4 batch-global fp64 sums of the control block
+                (32 bytes) once per iteration, so the global break (lma:118, gna:88, gda:84), the
+                "any rho > 0" gate (lma:110) and GD's batch-global fcon (gda:76) see the whole
+                batch and iteration counts match a single-device run of the reference.
+"""
+import torch
+import torch.distributed as dist
+
+
+def shard_bounds(B, world_size, rank):
+    """Contiguous [lo, hi) slice of rank; the first B % world_size ranks hold one extra problem."""
+    base, extra = divmod(B, world_size)
+    lo = rank * base + min(rank, extra)
+    return lo, lo + base + (1 if rank < extra else 0)
+
+
+def shard(t, world_size, rank, dim=0):
+    lo, hi = shard_bounds(t.shape[dim], world_size, rank)
+    return t.narrow(dim, lo, hi - lo)
+
+
+def make_reduce_hook(group=None):
+    """Hook for _engine.solve(reduce_hook=...): sums the control-block reductions over ranks."""
+    def hook(red):
+        dist.all_reduce(red, op=dist.ReduceOp.SUM, group=group)
+    return hook
+
+
+def gather_results(p_local, B_total, group=None):
+    """All-gather the per-rank [B_r, P] finals into the full [B_total, P] tensor on every rank
+    (one collective; shards may differ by one row, so they are padded to the largest)."""
+    world = dist.get_world_size(group)
+    P = p_local.shape[1]
+    rows = (B_total + world - 1) // world
+    pad = torch.zeros(rows, P, dtype=p_local.dtype, device=p_local.device)
+    pad[:p_local.shape[0]] = p_local
+    out = torch.empty(world * rows, P, dtype=p_local.dtype, device=p_local.device)
+    dist.all_gather_into_tensor(out, pad, group=group)
+    parts = []
+    for r in range(world):
+        lo, hi = shard_bounds(B_total, world, r)
+        parts.append(out[r * rows: r * rows + (hi - lo)])
+    return torch.cat(parts, dim=0)
+
+
+def solve_sharded(solver_fn, p_local, function, jac_function=None, args=(), wvec=None, mode='local',
+                  group=None, B_total=None, gather=True, **kw):
+    """Run one of the drop-in solvers on this rank's shard and (optionally) gather the finals.
+
+    solver_fn: lsq_lma_parallel | lsq_gna_parallel | gradient_descent_parallel
+    p_local / args: this rank's shard (use shard()/shard_bounds() to cut them)
+    returns (coeffs_list_local, p_full or None)"""
+    from .functions.parallel import _engine
+    if mode not in ('local', 'exact'):
+        raise ValueError("mode must be 'local' or 'exact'")
+    hook = make_reduce_hook(group) if (mode == 'exact' and dist.is_initialized() and dist.get_world_size(group) > 1) else None
+    if hook is None:
+        coeffs = solver_fn(p_local, function, jac_function, args=args, wvec=wvec, **kw)
+    else:
+        token = _engine.set_default_reduce_hook(hook)
+        try:
+            coeffs = solver_fn(p_local, function, jac_function, args=args, wvec=wvec, **kw)
+        finally:
+            _engine.set_default_reduce_hook(token)
+    full = None
+    if gather and dist.is_initialized() and dist.get_world_size(group) > 1:
+        if B_total is None:
+            n = torch.tensor([p_local.shape[0]], device=p_local.device)
+            dist.all_reduce(n, group=group)
+            B_total = int(n.item())
+        full = gather_results(p_local, B_total, group)
+    elif gather:
+        full = p_local
+    return coeffs, full
