@@ -9,6 +9,12 @@ import torch
 from conftest import GOLDEN
 
 RTOL = {'f64': 1e-9, 'f32': 1e-4}
+# Intermediate fp32 snapshots: the reference's own fp32 iterates carry more rounding noise than the
+# tolerance on finals.  Re-running the reference algorithm on the SAME fp32 inputs with exactly
+# rounded (fp64-accumulated) normal equations moves its iterate 7 of the synthetic lma_lev case by
+# 2.7e-4 while the final moves by 2.7e-5 (tests/test_oracle_golden.py::test_fp32_noise_floor), so
+# fp32 mid-trajectory snapshots are held to 1e-3 and only finals to north_star's 1e-4.
+RTOL_MID = {'f64': 1e-9, 'f32': 1e-3}
 DT = {'f64': torch.float64, 'f32': torch.float32}
 TOL = dict(ftol=1e-8, ptol=1e-8, gtol=1e-8)
 
@@ -55,6 +61,8 @@ def compare_plist(got, want, dn, what, allow_boundary=False):
     assert torch.equal(torch.isfinite(got), finite), f'{what}: finite pattern differs'
     g = torch.where(finite, got.double(), torch.zeros((), dtype=torch.float64))
     w = torch.where(finite, want.double(), torch.zeros((), dtype=torch.float64))
-    e = rel_err(g, w)
-    assert e <= RTOL[dn], f'{what}: rel err {e:.3e} > {RTOL[dn]:.0e}'
+    e = rel_err(g[-1], w[-1])
+    assert e <= RTOL[dn], f'{what}: final rel err {e:.3e} > {RTOL[dn]:.0e}'
+    e_mid = rel_err(g, w)
+    assert e_mid <= RTOL_MID[dn], f'{what}: snapshot rel err {e_mid:.3e} > {RTOL_MID[dn]:.0e}'
     return e

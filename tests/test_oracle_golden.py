@@ -122,3 +122,27 @@ def test_reference_reaches_ground_truth(fixtures):
     assert fixtures['lma_lev__f64__plist'].shape[0] < 100
     # Q6: Marquardt scaling stops after 3 iterations far from the optimum
     assert fixtures['lma_marq__f64__plist'].shape[0] == 3
+
+
+def test_fp32_noise_floor(synthetic, monkeypatch):
+    """Documents why fp32 mid-trajectory snapshots are held to RTOL_MID (helpers.py): the reference
+    algorithm itself, fed the same fp32 inputs but with exactly rounded normal equations, drifts from
+    the reference's own fp32 trajectory by more than 1e-4 mid-run and by less than 1e-4 at the end."""
+    dt = torch.float32
+    t, y, p0 = (torch.as_tensor(synthetic[k]).to(dt) for k in ('t', 'y', 'p0'))
+    w = torch.as_tensor(synthetic['wvec']).to(dt)
+    want = torch.as_tensor(synthetic['lma_lev__f32__plist'])
+    orig = O.normal_equations
+
+    def exact(f, J, wv):
+        g, H = orig(f.double(), J.double(), wv.double())
+        return g.to(f.dtype), H.to(f.dtype)
+
+    monkeypatch.setattr(O, 'normal_equations', exact)
+    _, kw = CASES['lma_lev']
+    got = torch.stack(O.lma(p0.clone(), M.emg_cost, M.emg_jac, args=(t, y), wvec=w, **kw).p_list)
+    k = min(got.shape[0], want.shape[0])
+    per_iter = torch.stack([torch.as_tensor(rel_err(got[i], want[i])) for i in range(k)])
+    assert float(per_iter.max()) > 1e-4          # the reference's fp32 iterates are noisier than 1e-4 ...
+    assert float(per_iter.max()) < 1e-3
+    assert float(per_iter[-1]) < 1e-4            # ... but its finals are not
