@@ -31,6 +31,32 @@ PLAIN = {'gna_plain': ('gna_plain', dict(l=.1, max_iter=25)),
          'gda_plain': ('gda_plain', dict(l=.1, max_iter=25))}
 
 
+# The reference's GD iteration on the synthetic batch (distinct data per cost, noise-dominated cost-summed
+# residual) never converges (99 = max_iter iterations) and is a chaotic map near the optimum: solving
+# the SAME fp64 least-squares problems through exact normal equations instead of QR — a 1e-16
+# perturbation per step — ends 4e-4 away from the reference (error doubles per iteration from
+# iteration ~17 on; tests/test_oracle_golden.py::test_gda_synthetic_is_chaotic).  No independent
+# implementation can match those finals, so these cases are held to: identical iteration count,
+# the first CHAOTIC_PREFIX snapshots at the normal tolerance, the whole trajectory inside the
+# attractor (CHAOTIC_BAND), and — in tests/test_gpu_parity.py — EVERY single step of the reference
+# trajectory reproduced from the reference's own previous iterate (teacher forcing) at RTOL.
+CHAOTIC = {'synthetic': ('gda', 'gda_l05')}
+CHAOTIC_PREFIX = 16
+CHAOTIC_BAND = 5e-3
+
+
+def compare_chaotic(got, want, dn, what):
+    want = torch.as_tensor(want)
+    got = (torch.stack(list(got)) if not torch.is_tensor(got) else got).cpu()
+    assert got.shape[0] == want.shape[0], f'{what}: iteration count {got.shape[0]} != reference {want.shape[0]}'
+    k = CHAOTIC_PREFIX
+    e = rel_err(got[:k], want[:k])
+    assert e <= RTOL_MID[dn], f'{what}: prefix rel err {e:.3e} > {RTOL_MID[dn]:.0e}'
+    band = rel_err(got, want)
+    assert band <= CHAOTIC_BAND, f'{what}: trajectory left the attractor band ({band:.3e})'
+    return e
+
+
 def load(name):
     return dict(np.load(os.path.join(GOLDEN, name + '.npz')))
 

@@ -7,7 +7,7 @@ in fp64, boundary flips reported in fp32."""
 import pytest
 import torch
 
-from helpers import CASES, PLAIN, DT, RTOL, load, compare_plist, rel_err
+from helpers import CASES, PLAIN, DT, RTOL, CHAOTIC, load, compare_plist, compare_chaotic, rel_err
 from oracle import nlls_oracle as O
 from oracle import models as M
 
@@ -202,7 +202,7 @@ def _torch_emg(n_costs):
     return (lambda p, t, y: M.emg_cost(p, t, y, n_costs=n_costs)), (lambda p, t, y: M.emg_jac(p, t, y, n_costs=n_costs))
 
 
-def _solve_case(gold, name, dn, fun, jac, args, prefix='', **extra):
+def _solve_case(gold, name, dn, fun, jac, args, prefix='', chaotic=False, **extra):
     key = f'{prefix}{name}__{dn}'
     if key + '__raises' in gold:
         pytest.skip('reference raises on this input (Marquardt overflow, Q6)')
@@ -212,6 +212,8 @@ def _solve_case(gold, name, dn, fun, jac, args, prefix='', **extra):
     w = cu(gold.get('wvec', [1.]), dt)
     pl = SOLVERS[solver](p, fun, jac, args=args, wvec=w, **kw, **extra)
     assert torch.equal(pl[-1], p), 'caller p must end as the final iterate (Q1)'
+    if chaotic:
+        return compare_chaotic(pl, gold[key + '__plist'], dn, key)
     return compare_plist(pl, gold[key + '__plist'], dn, key, allow_boundary=(dn == 'f32'))
 
 
@@ -244,7 +246,30 @@ def test_synthetic_cases_match_reference(name, dn, path):
     gold = load('synthetic')
     dt = DT[dn]
     fun, jac, extra = _emg_path(path, None)
-    _solve_case(gold, name, dn, fun, jac, (cu(gold['t'], dt), cu(gold['y'], dt)), **extra)
+    _solve_case(gold, name, dn, fun, jac, (cu(gold['t'], dt), cu(gold['y'], dt)), chaotic=name in CHAOTIC['synthetic'], **extra)
+
+
+@pytest.mark.parametrize('path', PATHS)
+@pytest.mark.parametrize('dn', ['f64', 'f32'])
+@pytest.mark.parametrize('name', list(CHAOTIC['synthetic']))
+def test_synthetic_gda_every_step_teacher_forced(name, dn, path):
+    """The chaotic GD cases (helpers.CHAOTIC): every step p_k = step(p_{k-1}) of the reference's
+    trajectory, started from the reference's own p_{k-1}, all K-1 steps solved as ONE batch."""
+    gold = load('synthetic')
+    dt = DT[dn]
+    _, kw = CASES[name]
+    traj = torch.as_tensor(gold[f'{name}__{dn}__plist'])                  # [K,B,P]
+    K, B, P = traj.shape
+    starts = torch.cat([torch.as_tensor(gold['p0'])[None].to(traj.dtype), traj[:-1]]).reshape(K * B, P)
+    y = torch.as_tensor(gold['y'])
+    y_rep = y[None].expand(K, *y.shape).reshape(K * B, *y.shape[1:])
+    fun, jac, extra = _emg_path(path, None)
+    p = cu(starts, dt).clone()
+    out = gradient_descent_parallel(p, fun, jac, args=(cu(gold['t'], dt), cu(y_rep, dt)), wvec=cu(gold['wvec'], dt),
+                                    **{**kw, 'max_iter': 1}, **extra)
+    assert len(out) == 1
+    e = rel_err(out[0].cpu().reshape(K, B, P), traj)
+    assert e <= RTOL[dn], f'{name}__{dn}: one-step rel err {e:.3e} > {RTOL[dn]:.0e}'
 
 
 @pytest.mark.parametrize('path', ['torch_callables', 'fused'])

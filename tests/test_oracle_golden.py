@@ -3,7 +3,7 @@ the unmodified reference (tests/golden/make_golden.py)."""
 import pytest
 import torch
 
-from helpers import CASES, PLAIN, DT, load, compare_plist, rel_err
+from helpers import CASES, PLAIN, DT, CHAOTIC_PREFIX, load, compare_plist, rel_err
 from oracle import nlls_oracle as O
 from oracle import models as M
 
@@ -146,3 +146,26 @@ def test_fp32_noise_floor(synthetic, monkeypatch):
     assert float(per_iter.max()) > 1e-4          # the reference's fp32 iterates are noisier than 1e-4 ...
     assert float(per_iter.max()) < 1e-3
     assert float(per_iter[-1]) < 1e-4            # ... but its finals are not
+
+
+def test_gda_synthetic_is_chaotic(synthetic, monkeypatch):
+    """Justifies helpers.CHAOTIC: the reference's GD on the synthetic batch amplifies a 1e-16 per-step
+    perturbation (QR replaced by exact fp64 normal equations, cond(j) < 60) to > 1e-5 by max_iter."""
+    dt = torch.float64
+    t, y, p0 = (torch.as_tensor(synthetic[k]).to(dt) for k in ('t', 'y', 'p0'))
+    w = torch.as_tensor(synthetic['wvec']).to(dt)
+    want = torch.as_tensor(synthetic['gda__f64__plist'])
+    orig = O.solve_fp64
+
+    def via_normal_equations(A, b, out_dtype):
+        if A.dim() == 3 and A.shape[1] > A.shape[2]:
+            At = A.double().transpose(1, 2)
+            return torch.linalg.solve(At @ A.double(), (At @ b.double()[..., None])[..., 0]).to(out_dtype)
+        return orig(A, b, out_dtype)
+
+    monkeypatch.setattr(O, 'solve_fp64', via_normal_equations)
+    _, kw = CASES['gda']
+    got = torch.stack(O.gda(p0.clone(), M.emg_cost, M.emg_jac, args=(t, y), wvec=w, **kw).p_list)
+    assert got.shape[0] == want.shape[0] == kw['max_iter']
+    assert rel_err(got[:CHAOTIC_PREFIX], want[:CHAOTIC_PREFIX]) <= 1e-9
+    assert rel_err(got[-1], want[-1]) > 1e-5
