@@ -174,27 +174,60 @@ def test_skewgauss_callables_match_oracle(dn, P):
     assert (J.cpu() - J0).abs().max() <= tol * J0.abs().max()
 
 
+@pytest.mark.parametrize('force_direct', [False, True])
+@pytest.mark.parametrize('n_keep', [256, 250, 251, 37])
+@pytest.mark.parametrize('shared_y', [False, True])
 @pytest.mark.parametrize('dn', ['f64', 'f32'])
-def test_fused_normal_eq_matches_oracle(dn):
+def test_fused_normal_eq_matches_oracle(dn, shared_y, n_keep, force_direct):
+    """K4 (bulk-copy staged and direct variants; ragged N falls back to direct by itself) on two
+    consecutive iterations: the second reads the first's f as f_prev through the ping-pong buffers."""
     gold = load('synthetic')
     dt = DT[dn]
-    p, t, y, w = cu(gold['p0'], dt), cu(gold['t'], dt), cu(gold['y'], dt), cu(gold['wvec'], dt)
+    lo = (gold['t'].shape[0] - n_keep) // 2                  # centred window: the peak sits mid-range
+    p, t, w = cu(gold['p0'], dt), cu(gold['t'][lo:lo + n_keep], dt), cu(gold['wvec'], dt)
+    y = cu(gold['y'][:, :, lo:lo + n_keep], dt).contiguous()
     B, C, N = y.shape
+    if shared_y:
+        y = y[:, 0].contiguous()
+        ybs, ycs = N, 0
+    else:
+        ybs, ycs = C * N, N
     g = torch.empty(B, 4, dtype=dt, device=DEV)
     H = torch.empty(B, 4, 4, dtype=dt, device=DEV)
     st = torch.empty(B, 4, dtype=torch.float64, device=DEV)
     fpp = torch.zeros(2, B, C, N, dtype=dt, device=DEV)
-    _lib.call('nlls_model_normal_eq', _lib.MODEL_EMG, _lib.dtype_code(p), _lib.ptr(p), 4, _lib.ptr(t), _lib.ptr(y), C * N, N,
-              _lib.ptr(w), C, B, C, N, _lib.ptr(fpp[0]), _lib.ptr(fpp[1]), _lib.ptr(g), _lib.ptr(H), _lib.ptr(st), None,
-              _lib.stream_ptr())
-    pc, tc, yc, wc = p.cpu().double(), t.cpu().double(), y.cpu().double(), w.cpu().double()
-    f0, J0 = M.emg_cost(pc, tc, yc), M.emg_jac(pc, tc, yc)
-    g0, H0 = O.normal_equations(f0, J0, wc)
+    ctrl = _lib.new_ctrl(DEV)
+    lib = _lib.load()
+    old = lib.nlls_set_force_direct(1 if force_direct else 0)
+    try:
+        ps = [p, (p * 1.01).contiguous()]
+        outs = []
+        for it in range(2):
+            ctrl.view(torch.int32)[1] = it
+            _lib.call('nlls_model_normal_eq', _lib.MODEL_EMG, _lib.dtype_code(p), _lib.ptr(ps[it]), 4, _lib.ptr(t), _lib.ptr(y),
+                      ybs, ycs, _lib.ptr(w), C, B, C, N, _lib.ptr(fpp[0]), _lib.ptr(fpp[1]), _lib.ptr(g), _lib.ptr(H),
+                      _lib.ptr(st), _lib.ptr(ctrl), _lib.stream_ptr())
+            torch.cuda.synchronize()
+            outs.append((g.cpu().double(), H.cpu().double(), st.cpu().clone(), fpp[it].cpu().double()))
+    finally:
+        lib.nlls_set_force_direct(old)
+    tc, yc, wc = t.cpu().double(), y.cpu().double(), w.cpu().double()
     tol = 1e-11 if dn == 'f64' else 5e-4
-    assert (g.cpu().double() - g0).abs().max() <= tol * g0.abs().max()
-    assert (H.cpu().double() - H0).abs().max() <= tol * H0.abs().max()
-    assert torch.allclose(st[:, 0].cpu(), O.cost_sum_stat(f0), rtol=1e-11 if dn == 'f64' else 1e-3)
-    assert torch.allclose(fpp[0].cpu().double(), f0, rtol=1e-11 if dn == 'f64' else 1e-3, atol=1e-12 if dn == 'f64' else 1e-7)
+    f_last = None
+    for it in range(2):
+        pc = ps[it].cpu().double()
+        f0, J0 = M.emg_cost(pc, tc, yc, n_costs=C if shared_y else None), M.emg_jac(pc, tc, yc, n_costs=C if shared_y else None)
+        g0, H0 = O.normal_equations(f0, J0, wc)
+        gg, HH, ss, ff = outs[it]
+        assert (gg - g0).abs().max() <= tol * g0.abs().max()
+        assert (HH - H0).abs().max() <= tol * H0.abs().max()
+        rt = 1e-11 if dn == 'f64' else 1e-3
+        assert torch.allclose(ss[:, 0], O.cost_sum_stat(f0), rtol=rt)
+        assert torch.allclose(ss[:, 2], (f0 ** 2).sum((1, 2)), rtol=rt)
+        assert torch.allclose(ff, f0, rtol=rt, atol=1e-12 if dn == 'f64' else 1e-7)
+        if it == 1:
+            assert torch.allclose(ss[:, 1], ((f_last - ff) ** 2).sum((1, 2)), rtol=1e-9 if dn == 'f64' else 1e-3)
+        f_last = ff
 
 
 # ------------------------------------------------------------------------------ solvers

@@ -25,6 +25,8 @@ inline int check_launch(const char* what) {
 
 inline bool aligned_to(const void* p, size_t a) { return (reinterpret_cast<uintptr_t>(p) % a) == 0; }
 
+extern int g_force_direct;    // test/bench hook (nlls_set_force_direct): 1 = never take a bulk-copy staged kernel
+
 constexpr int kNumSMs = 148;   // B200: 2 dies x 74 SMs; grids are sized in multiples of this
 
 // --------------------------------------------------------------------------- device side

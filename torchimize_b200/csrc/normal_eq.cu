@@ -558,7 +558,7 @@ static int occupancy_grid(K kernel, int tpb, size_t smem, long long B) {
   return (int)grid;
 }
 
-static int g_force_direct = 0;   // test/bench hook: NLLS_FORCE_DIRECT=1 disables the staged kernel
+int g_force_direct = 0;          // test/bench hook: NLLS_FORCE_DIRECT=1 disables the staged kernels
 
 template <typename T, int P>
 static int launch_normal_eq_p(const T* J, const T* f, const T* fprev, const T* w, int wlen, long long B, int C, int N,
