@@ -58,6 +58,29 @@ __device__ __forceinline__ void warp_sum_many(T (&v)[V]) {
   for (int k = 0; k < V; ++k) v[k] = warp_sum(v[k]);
 }
 
+// Transposed ("recursive halving") warp reduction of VP values held by every lane, VP a power of
+// two <= 32: VP - 1 + log2(32/VP) shuffles instead of 5*VP butterflies.  On return v[0] of lane L
+// holds the warp total of value index L >> log2(32/VP); lanes with (L & (32/VP - 1)) == 0 own it.
+template <int VP>
+__device__ __forceinline__ void warp_reduce_transpose(double (&v)[VP]) {
+  static_assert(VP >= 1 && VP <= 32 && (VP & (VP - 1)) == 0, "VP must be a power of two <= 32");
+  const int lane = threadIdx.x & 31;
+  int m = 16;
+#pragma unroll
+  for (int n = VP; n > 1; n >>= 1, m >>= 1) {
+    const bool upper = (lane & m) != 0;
+#pragma unroll
+    for (int i = 0; i < n / 2; ++i) {
+      const double keep = upper ? v[i + n / 2] : v[i];
+      const double send = upper ? v[i] : v[i + n / 2];
+      v[i] = keep + shfl_xor(send, m);
+    }
+  }
+#pragma unroll
+  for (; m > 0; m >>= 1) v[0] += shfl_xor(v[0], m);
+}
+template <int V> struct Pow2Ceil { static constexpr int value = V <= 1 ? 1 : V <= 2 ? 2 : V <= 4 ? 4 : V <= 8 ? 8 : V <= 16 ? 16 : 32; };
+
 // streaming (read-once) global loads: bypass L1 allocation
 __device__ __forceinline__ double ldg_stream(const double* p) {
   double r;

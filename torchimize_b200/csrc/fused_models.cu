@@ -135,19 +135,22 @@ k_model_normal_eq(const T* __restrict__ p, const T* __restrict__ x, const T* __r
 // ------------------------------------------------------------------ fused normal equations, bulk-copy staged
 // Same arithmetic as k_model_normal_eq, but the data rows y[b,c,n0:n0+TN] and f_prev[b,c,n0:n0+TN]
 // of a tile are brought into shared memory by 1-D bulk async copies (cp.async.bulk -> UBLKCP,
-// completion on one mbarrier per stage) issued NSTAGE-1 tiles ahead by one elected thread, across
+// completion on one mbarrier per stage) issued NSTAGE tiles ahead by one elected thread, across
 // problem boundaries.  The r01a profile of the direct kernel showed 73 % of its stalls on the
 // scoreboard of the y / f_prev loads (profiles/r01a_fused_baseline.txt): the loads sat in the
 // dependent chain of each sample.  Here the bytes in flight per SM no longer depend on registers
-// or occupancy.  TN = TPB * S samples per tile.
-template <typename T, typename Model, int TPB, int S>
+// or occupancy.  TN = TPB * S samples per tile.  One __syncthreads per tile (stage hand-back) and
+// one per problem (cross-warp sums, double-buffered); the per-problem warp sums use the
+// transposed reduction (16 shuffles for P = 4 instead of 80).
+template <typename T, typename Model, int TPB, int S, int NSTAGE>
 __global__ void __launch_bounds__(TPB)
 k_model_normal_eq_staged(const T* __restrict__ p, const T* __restrict__ x, const T* __restrict__ y, long long ybs,
                          long long ycs, const T* __restrict__ w, int wlen, long long B, int C, int N, T* fA, T* fB,
-                         T* __restrict__ g, T* __restrict__ H, double* __restrict__ stats, const nlls_ctrl* ctrl,
-                         int nstage) {
+                         T* __restrict__ g, T* __restrict__ H, double* __restrict__ stats, const nlls_ctrl* ctrl) {
   if (is_done(ctrl)) return;
   constexpr int P = Model::P, NW = TPB / 32, NH = Tri<P>::N, V = P + NH + 2, TN = TPB * S;
+  constexpr int VP = Pow2Ceil<V>::value, OWN = 32 / VP;      // transposed reduction: lane L owns value L / OWN
+  static_assert(V <= 32, "model with too many parameters for the transposed reduction");
   const int it = iter_index(ctrl);
   T* __restrict__ f_out = (it & 1) ? fB : fA;
   const T* __restrict__ f_prev = (it > 0 && fA) ? ((it & 1) ? fA : fB) : nullptr;
@@ -156,51 +159,57 @@ k_model_normal_eq_staged(const T* __restrict__ p, const T* __restrict__ x, const
   const int stage_elems = (Cy + C) * TN;                     // [Cy][TN] data rows then [C][TN] f_prev rows
   extern __shared__ __align__(128) unsigned char smem_raw[];
   T* ring = reinterpret_cast<T*>(smem_raw);
-  size_t off = (size_t)nstage * stage_elems * sizeof(T);
+  size_t off = (size_t)NSTAGE * stage_elems * sizeof(T);
   off = (off + 15) & ~(size_t)15;
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem_raw + off);
-  double* red = reinterpret_cast<double*>(smem_raw + off + 8 * 8);   // up to 8 stages of barriers
-  double* sfc = red + NW * V;                                // [C][TPB]
-  double* sfw = sfc + (size_t)C * TPB;                       // [C][NW]
+  double* red = reinterpret_cast<double*>(smem_raw + off + 8 * 8);   // [2][NW][VP]
+  double* sfc = red + 2 * NW * VP;                           // [2][C][TPB] per-thread per-cost sums of f
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
 
   if (tid == 0) {
-    for (int s = 0; s < nstage; ++s) mbar_init(&bars[s], 1);
+#pragma unroll
+    for (int s = 0; s < NSTAGE; ++s) mbar_init(&bars[s], 1);
     mbar_fence_init();
   }
   __syncthreads();
 
-  const int TPP = (N + TN - 1) / TN;                         // tiles per problem
-  const long long my_problems = (B - blockIdx.x + gridDim.x - 1) / gridDim.x;
-  const long long total_tiles = my_problems * TPP;
-  auto issue = [&](long long t) {                            // thread 0 only
-    if (t >= total_tiles) return;
-    const long long b = blockIdx.x + (t / TPP) * gridDim.x;
-    const int n0 = (int)(t % TPP) * TN;
-    const int rows = min(TN, N - n0);
+  // ---- producer state (thread 0): next tile to issue = (problem pb, sample offset pn0) into stage pst
+  long long pb = blockIdx.x;
+  int pn0 = 0, pst = 0;
+  auto issue = [&]() {
+    if (pb >= B) return;
+    const int rows = min(TN, N - pn0);
     const unsigned bytes = (unsigned)rows * (unsigned)sizeof(T);
-    const int st = (int)(t % nstage);
-    T* dst = ring + (size_t)st * stage_elems;
-    mbar_expect_tx(&bars[st], bytes * (unsigned)(Cy + (has_prev ? C : 0)));
-    const T* yb = y + b * ybs + n0;
-    for (int c = 0; c < Cy; ++c) bulk_g2s(dst + c * TN, yb + c * ycs, bytes, &bars[st]);
+    T* dst = ring + (size_t)pst * stage_elems;
+    uint64_t* bar = &bars[pst];
+    mbar_expect_tx(bar, bytes * (unsigned)(Cy + (has_prev ? C : 0)));
+    const T* src = y + pb * ybs + pn0;
+    for (int c = 0; c < Cy; ++c, src += ycs, dst += TN) bulk_g2s(dst, src, bytes, bar);
     if (has_prev) {
-      const T* pb = f_prev + b * (long long)C * N + n0;
-      for (int c = 0; c < C; ++c) bulk_g2s(dst + (Cy + c) * TN, pb + (long long)c * N, bytes, &bars[st]);
+      const T* ps = f_prev + pb * (long long)C * N + pn0;
+      for (int c = 0; c < C; ++c, ps += N, dst += TN) bulk_g2s(dst, ps, bytes, bar);
     }
+    pn0 += TN;
+    if (pn0 >= N) { pn0 = 0; pb += gridDim.x; }
+    pst = (pst + 1 == NSTAGE) ? 0 : pst + 1;
   };
-  if (tid == 0)
-    for (int s = 0; s < nstage; ++s) issue(s);
+  if (tid == 0) {
+#pragma unroll
+    for (int s = 0; s < NSTAGE; ++s) issue();
+  }
 
-  long long t = 0;
-  for (long long b = blockIdx.x; b < B; b += gridDim.x) {
+  int st = 0, pbuf = 0;
+  unsigned ph = 0;
+  for (long long b = blockIdx.x; b < B; b += gridDim.x, pbuf ^= 1) {
     Model M;
     M.load(p + b * P);
     RowAcc<T, P> acc;
     acc.clear();
     double sd = 0.0, sq = 0.0;
-    for (int c = 0; c < C; ++c) sfc[c * TPB + tid] = 0.0;
-    for (int n0 = 0; n0 < N; n0 += TN, ++t) {
+    double* my_sfc = sfc + (size_t)pbuf * C * TPB + tid;
+    for (int c = 0; c < C; ++c) my_sfc[c * TPB] = 0.0;
+    T* fo_b = f_out ? f_out + b * (long long)C * N : nullptr;
+    for (int n0 = 0; n0 < N; n0 += TN) {
       T m[S], k[S][P], s2[S], s3[S];
 #pragma unroll
       for (int i = 0; i < S; ++i) {
@@ -209,26 +218,23 @@ k_model_normal_eq_staged(const T* __restrict__ p, const T* __restrict__ x, const
         s2[i] = T(0);
         s3[i] = T(0);
       }
-      const int st = (int)(t % nstage);
-      mbar_wait(&bars[st], (unsigned)((t / nstage) & 1));
-      const T* sy = ring + (size_t)st * stage_elems;
-      const T* sp = sy + Cy * TN;
+      mbar_wait(&bars[st], ph);
+      const T* yc = ring + (size_t)st * stage_elems + tid;
+      const T* pc = yc + Cy * TN;
+      const int ystep = (Cy == 1) ? 0 : TN;
+      T* fo = fo_b ? fo_b + n0 + tid : nullptr;
 #pragma unroll 2
-      for (int c = 0; c < C; ++c) {
+      for (int c = 0; c < C; ++c, yc += ystep, pc += TN) {
         const T wc = w[wlen == 1 ? 0 : c];
-        const T* yc = sy + (Cy == 1 ? 0 : c) * TN;
-        const T* pc = sp + c * TN;
-        const long long seg = (b * C + c) * (long long)N;
         double sfl = 0.0;
 #pragma unroll
         for (int i = 0; i < S; ++i) {
-          const int j = i * TPB + tid, n = n0 + j;
-          if (n < N) {
-            const T r = yc[j] - m[i];
+          if (n0 + i * TPB + tid < N) {
+            const T r = yc[i * TPB] - m[i];
             const T fv = r * r;
-            if (f_out) stg_stream(f_out + seg + n, fv);
+            if (fo) stg_stream(fo + i * TPB, fv);
             if (has_prev) {
-              const T d = pc[j] - fv;
+              const T d = pc[i * TPB] - fv;
               sd = fma((double)d, (double)d, sd);
             }
             sq = fma((double)fv, (double)fv, sq);
@@ -238,37 +244,37 @@ k_model_normal_eq_staged(const T* __restrict__ p, const T* __restrict__ x, const
             s3[i] = fma(wf, r, s3[i]);
           }
         }
-        sfc[c * TPB + tid] += sfl;
+        my_sfc[c * TPB] += sfl;
+        if (fo) fo += N;
       }
 #pragma unroll
-      for (int i = 0; i < S; ++i) {
-        const int n = n0 + i * TPB + tid;
-        if (n < N) acc.add_scaled(k[i], T(2) * s3[i], T(4) * s2[i]);
+      for (int i = 0; i < S; ++i)
+        if (n0 + i * TPB + tid < N) acc.add_scaled(k[i], T(2) * s3[i], T(4) * s2[i]);
+      if (n0 + TN < N) {
+        __syncthreads();                                     // every thread is done with this stage
+        if (tid == 0) issue();
       }
-      __syncthreads();                                       // every thread is done with this stage
-      if (tid == 0) issue(t + nstage);
+      if (++st == NSTAGE) { st = 0; ph ^= 1u; }
     }
-    acc.warp_reduce();
-    sd = warp_sum(sd);
-    sq = warp_sum(sq);
-    for (int c = 0; c < C; ++c) {
-      const double s = warp_sum(sfc[c * TPB + tid]);
-      if (lane == 0) sfw[c * NW + warp] = s;
-    }
-    if (lane == 0) {
-      double* r = red + warp * V;
+    // ---- per-problem sums: transposed warp reduction, then fp64 across warps through smem
+    double v[VP];
 #pragma unroll
-      for (int i = 0; i < P; ++i) r[i] = (double)acc.g[i];
+    for (int i = 0; i < P; ++i) v[i] = (double)acc.g[i];
 #pragma unroll
-      for (int i = 0; i < NH; ++i) r[P + i] = (double)acc.h[i];
-      r[P + NH] = sd;
-      r[P + NH + 1] = sq;
-    }
-    __syncthreads();
+    for (int i = 0; i < NH; ++i) v[P + i] = (double)acc.h[i];
+    v[P + NH] = sd;
+    v[P + NH + 1] = sq;
+#pragma unroll
+    for (int i = V; i < VP; ++i) v[i] = 0.0;
+    warp_reduce_transpose<VP>(v);
+    double* myred = red + (size_t)pbuf * NW * VP;
+    if ((lane & (OWN - 1)) == 0) myred[warp * VP + lane / OWN] = v[0];
+    __syncthreads();                                         // last tile's stage is free; red and sfc are complete
+    if (tid == 0) issue();
     if (tid < V) {
       double s = 0.0;
 #pragma unroll
-      for (int kk = 0; kk < NW; ++kk) s += red[kk * V + tid];
+      for (int kk = 0; kk < NW; ++kk) s += myred[kk * VP + tid];
       if (tid < P) {
         g[b * P + tid] = (T)s;
       } else if (tid < P + NH) {
@@ -280,17 +286,21 @@ k_model_normal_eq_staged(const T* __restrict__ p, const T* __restrict__ x, const
       } else {
         stats[b * 4 + (tid - P - NH) + 1] = s;
       }
-    } else if (tid == V) {
+    } else if (warp == NW - 1) {                             // sum_c (sum_n f)^2 from the per-thread sums
+      const double* col = sfc + (size_t)pbuf * C * TPB;
       double tot = 0.0;
       for (int c = 0; c < C; ++c) {
         double s = 0.0;
-        for (int kk = 0; kk < NW; ++kk) s += sfw[c * NW + kk];
+#pragma unroll
+        for (int kk = 0; kk < NW; ++kk) s += col[c * TPB + kk * 32 + lane];
+        s = warp_sum(s);
         tot = fma(s, s, tot);
       }
-      stats[b * 4 + 0] = tot;
-      stats[b * 4 + 3] = 0.0;
+      if (lane == 0) {
+        stats[b * 4 + 0] = tot;
+        stats[b * 4 + 3] = 0.0;
+      }
     }
-    __syncthreads();
   }
 }
 
@@ -485,21 +495,24 @@ static int run_op(Op op, const ModelArgs& a) {
       const size_t smem = ((size_t)NW * V + (size_t)a.C * TPB + (size_t)a.C * NW) * 8;
       if (smem > 200 * 1024) { set_error("fused model path: too many costs (C=%d)", a.C); return NLLS_E_SHAPE; }
       {   // bulk-copy staged variant whenever every data row is 16-byte addressable
-        constexpr int TPB2 = 256, S2 = 2, NW2 = TPB2 / 32, TN = TPB2 * S2;
+        constexpr int TPB2 = 256, S2 = 2, NW2 = TPB2 / 32, TN = TPB2 * S2, VP = Pow2Ceil<V>::value;
         const size_t es = sizeof(T);
         const int Cy = a.ycs == 0 ? 1 : a.C;
         const size_t stage = (size_t)(Cy + a.C) * TN * es;
-        const size_t tail = 64 + ((size_t)NW2 * V + (size_t)a.C * TPB2 + (size_t)a.C * NW2) * 8;
+        const size_t tail = 16 + 64 + ((size_t)2 * NW2 * VP + (size_t)2 * a.C * TPB2) * 8;
         const bool ok16 = aligned_to(a.y, 16) && (a.ybs * es) % 16 == 0 && (a.ycs * es) % 16 == 0 && ((size_t)a.N * es) % 16 == 0 &&
                           (!a.fA || (aligned_to(a.fA, 16) && aligned_to(a.fB, 16))) && !g_force_direct;
         // 3 stages when two CTAs of them still fit one SM, else 2
-        int nstage = (2 * (3 * stage + tail + 1024) <= 220 * 1024) ? 3 : 2;
-        const size_t smem2 = nstage * stage + 16 + tail;
+        const bool three = 2 * (3 * stage + tail + 1024) <= 226 * 1024;
+        const size_t smem2 = (three ? 3 : 2) * stage + tail;
         if (ok16 && smem2 <= 220 * 1024) {
-          auto kern2 = k_model_normal_eq_staged<T, Model, TPB2, S2>;
-          const int grid2 = grid_for(kern2, TPB2, smem2, a.B);
-          kern2<<<grid2, TPB2, smem2, a.st>>>((const T*)a.p, (const T*)a.x, (const T*)a.y, a.ybs, a.ycs, (const T*)a.w, a.wlen,
-                                              a.B, a.C, a.N, (T*)a.fA, (T*)a.fB, (T*)a.g, (T*)a.H, a.stats, a.ctrl, nstage);
+          auto launch = [&](auto kern2) {
+            const int grid2 = grid_for(kern2, TPB2, smem2, a.B);
+            kern2<<<grid2, TPB2, smem2, a.st>>>((const T*)a.p, (const T*)a.x, (const T*)a.y, a.ybs, a.ycs, (const T*)a.w, a.wlen,
+                                                a.B, a.C, a.N, (T*)a.fA, (T*)a.fB, (T*)a.g, (T*)a.H, a.stats, a.ctrl);
+          };
+          if (three) launch(k_model_normal_eq_staged<T, Model, TPB2, S2, 3>);
+          else launch(k_model_normal_eq_staged<T, Model, TPB2, S2, 2>);
           return check_launch("nlls_model_normal_eq(staged)");
         }
       }
