@@ -108,6 +108,7 @@ __device__ __forceinline__ float2 ldg_stream2(const float* p) {
   asm volatile("ld.global.nc.L1::no_allocate.v2.f32 {%0,%1}, [%2];" : "=f"(r.x), "=f"(r.y) : "l"(p));
   return r;
 }
+__device__ __forceinline__ void prefetch_l1(const void* p) { asm volatile("prefetch.global.L1 [%0];" ::"l"(p)); }
 // streaming stores (written once, read by a later kernel)
 __device__ __forceinline__ void stg_stream(double* p, double v) {
   asm volatile("st.global.L1::no_allocate.f64 [%0], %1;" ::"l"(p), "d"(v) : "memory");

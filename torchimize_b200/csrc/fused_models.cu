@@ -9,6 +9,7 @@
 //     H   = sum_n k k^T (4 sum_c w_c r_c^2)
 // (newton_parallel.py:40-43 applied to tests/unit_test_parallel.py:53-65,105-118).  HBM traffic per
 // iteration: y once, f_prev once (read), f once (write) — 3*s*C*N bytes per problem.
+#include <cstdlib>
 #include "models.cuh"
 #include "rowacc.cuh"
 
@@ -203,6 +204,7 @@ k_model_normal_eq_staged(const T* __restrict__ p, const T* __restrict__ x, const
   for (long long b = blockIdx.x; b < B; b += gridDim.x, pbuf ^= 1) {
     Model M;
     M.load(p + b * P);
+    if (tid == 0 && b + gridDim.x < B) prefetch_l1(p + (b + gridDim.x) * P);   // next problem's parameters
     RowAcc<T, P> acc;
     acc.clear();
     double sd = 0.0, sq = 0.0;
@@ -487,6 +489,40 @@ struct ModelArgs {
 
 enum Op { OP_NEQ, OP_NEQ_GDA, OP_COST, OP_EVAL };
 
+// tuning hook: NLLS_FUSED_VARIANT selects the (threads, samples per thread) shape of the staged fused kernel
+static int fused_variant() {
+  static int v = -1;
+  if (v < 0) { const char* e = getenv("NLLS_FUSED_VARIANT"); v = e ? atoi(e) : 0; }
+  return v;
+}
+
+// returns 0 when launched, 1 when the shape is not eligible for bulk copies, or a launch error
+template <typename T, typename Model, int TPB2, int S2>
+static int launch_staged(const ModelArgs& a) {
+  constexpr int P = Model::P, V = P + Tri<P>::N + 2, NW2 = TPB2 / 32, TN = TPB2 * S2, VP = Pow2Ceil<V>::value;
+  const size_t es = sizeof(T);
+  const int Cy = a.ycs == 0 ? 1 : a.C;
+  const size_t stage = (size_t)(Cy + a.C) * TN * es;
+  const size_t tail = 16 + 64 + ((size_t)2 * NW2 * VP + (size_t)2 * a.C * TPB2) * 8;
+  const bool ok16 = aligned_to(a.y, 16) && (a.ybs * es) % 16 == 0 && (a.ycs * es) % 16 == 0 && ((size_t)a.N * es) % 16 == 0 &&
+                    (!a.fA || (aligned_to(a.fA, 16) && aligned_to(a.fB, 16)));
+  if (!ok16) return 1;
+  // as many CTAs per SM as registers allow (64K regs / (128 regs x TPB2)); 3 stages if they still fit, else 2
+  const int want_ctas = 512 / TPB2;
+  const bool three = (size_t)want_ctas * (3 * stage + tail + 1024) <= 226 * 1024;
+  const size_t smem2 = (three ? 3 : 2) * stage + tail;
+  if (smem2 > 220 * 1024) return 1;
+  auto launch = [&](auto kern2) {
+    const int grid2 = grid_for(kern2, TPB2, smem2, a.B);
+    kern2<<<grid2, TPB2, smem2, a.st>>>((const T*)a.p, (const T*)a.x, (const T*)a.y, a.ybs, a.ycs, (const T*)a.w, a.wlen,
+                                        a.B, a.C, a.N, (T*)a.fA, (T*)a.fB, (T*)a.g, (T*)a.H, a.stats, a.ctrl);
+  };
+  if (three) launch(k_model_normal_eq_staged<T, Model, TPB2, S2, 3>);
+  else launch(k_model_normal_eq_staged<T, Model, TPB2, S2, 2>);
+  return check_launch("nlls_model_normal_eq(staged)");
+}
+
+
 template <typename T, typename Model>
 static int run_op(Op op, const ModelArgs& a) {
   constexpr int TPB = kFusedTPB, S = kFusedS, NW = TPB / 32, P = Model::P, V = P + Tri<P>::N + 2;
@@ -494,27 +530,15 @@ static int run_op(Op op, const ModelArgs& a) {
     case OP_NEQ: {
       const size_t smem = ((size_t)NW * V + (size_t)a.C * TPB + (size_t)a.C * NW) * 8;
       if (smem > 200 * 1024) { set_error("fused model path: too many costs (C=%d)", a.C); return NLLS_E_SHAPE; }
-      {   // bulk-copy staged variant whenever every data row is 16-byte addressable
-        constexpr int TPB2 = 256, S2 = 2, NW2 = TPB2 / 32, TN = TPB2 * S2, VP = Pow2Ceil<V>::value;
-        const size_t es = sizeof(T);
-        const int Cy = a.ycs == 0 ? 1 : a.C;
-        const size_t stage = (size_t)(Cy + a.C) * TN * es;
-        const size_t tail = 16 + 64 + ((size_t)2 * NW2 * VP + (size_t)2 * a.C * TPB2) * 8;
-        const bool ok16 = aligned_to(a.y, 16) && (a.ybs * es) % 16 == 0 && (a.ycs * es) % 16 == 0 && ((size_t)a.N * es) % 16 == 0 &&
-                          (!a.fA || (aligned_to(a.fA, 16) && aligned_to(a.fB, 16))) && !g_force_direct;
-        // 3 stages when two CTAs of them still fit one SM, else 2
-        const bool three = 2 * (3 * stage + tail + 1024) <= 226 * 1024;
-        const size_t smem2 = (three ? 3 : 2) * stage + tail;
-        if (ok16 && smem2 <= 220 * 1024) {
-          auto launch = [&](auto kern2) {
-            const int grid2 = grid_for(kern2, TPB2, smem2, a.B);
-            kern2<<<grid2, TPB2, smem2, a.st>>>((const T*)a.p, (const T*)a.x, (const T*)a.y, a.ybs, a.ycs, (const T*)a.w, a.wlen,
-                                                a.B, a.C, a.N, (T*)a.fA, (T*)a.fB, (T*)a.g, (T*)a.H, a.stats, a.ctrl);
-          };
-          if (three) launch(k_model_normal_eq_staged<T, Model, TPB2, S2, 3>);
-          else launch(k_model_normal_eq_staged<T, Model, TPB2, S2, 2>);
-          return check_launch("nlls_model_normal_eq(staged)");
+      if (!g_force_direct) {   // bulk-copy staged variant whenever every data row is 16-byte addressable
+        int rc = 1;
+        switch (fused_variant()) {
+          case 1: rc = launch_staged<T, Model, 256, 2>(a); break;
+          case 2: rc = launch_staged<T, Model, 64, 2>(a); break;
+          case 3: rc = launch_staged<T, Model, 64, 4>(a); break;
+          default: rc = launch_staged<T, Model, 128, 2>(a); break;   // 4 CTAs/SM: best of the r01 sweep (profiles/)
         }
+        if (rc <= 0) return rc;                              // 0 launched, < 0 error, 1 = shape not eligible
       }
       auto kern = k_model_normal_eq<T, Model, TPB, S>;
       const int grid = grid_for(kern, TPB, smem, a.B);
