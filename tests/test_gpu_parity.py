@@ -305,6 +305,22 @@ def test_synthetic_gda_every_step_teacher_forced(name, dn, path):
     assert e <= RTOL[dn], f'{name}__{dn}: one-step rel err {e:.3e} > {RTOL[dn]:.0e}'
 
 
+@pytest.mark.parametrize('dn', ['f64', 'f32'])
+@pytest.mark.parametrize('name', ['lma_lev', 'gna', 'gda'])
+def test_fixture_cases_fused_direct_kernels(name, dn):
+    """Same as test_fixture_cases_match_reference[fused] but with the bulk-copy staged kernels switched off,
+    so the direct-load fallbacks (unaligned shapes) stay covered at solver level."""
+    gold = load('fixtures')
+    dt = DT[dn]
+    fun, jac, extra = _emg_path('fused', 2)
+    lib = _lib.load()
+    old = lib.nlls_set_force_direct(1)
+    try:
+        _solve_case(gold, name, dn, fun, jac, (cu(gold['t'], dt), cu(gold['y'], dt)), **extra)
+    finally:
+        lib.nlls_set_force_direct(old)
+
+
 @pytest.mark.parametrize('path', ['torch_callables', 'fused'])
 @pytest.mark.parametrize('dn', ['f64', 'f32'])
 @pytest.mark.parametrize('name', ['lma_lev', 'gna', 'gda'])

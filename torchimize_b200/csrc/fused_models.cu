@@ -133,6 +133,69 @@ k_model_normal_eq(const T* __restrict__ p, const T* __restrict__ x, const T* __r
   }
 }
 
+// ------------------------------------------------------------------ shared tile ring (bulk-copy producer)
+// One elected thread streams, NSTAGE tiles ahead and across problem boundaries, up to two row
+// sets per tile into a shared-memory stage: set A = nA rows a[b*a_bs + r*a_rs + n0 .. +rows],
+// set B = nB rows likewise (nB = 0 when absent).  Stage layout: [nA][TN] then [nB][TN] elements.
+template <typename T, int TN, int NSTAGE>
+struct TileRing {
+  T* ring;
+  uint64_t* bars;
+  const T *a, *bsrc;
+  long long a_bs, a_rs, b_bs, b_rs, B;
+  int nA, nB, N, stage_elems;
+  long long pb;          // producer: next problem
+  int pn0, pst;          // producer: next sample offset, next stage
+  int st;                // consumer: current stage
+  unsigned ph;           // consumer: current parity
+  __device__ __forceinline__ void init(unsigned char* smem, const T* a_, long long a_bs_, long long a_rs_, int nA_,
+                                       const T* b_, long long b_bs_, long long b_rs_, int nB_, long long B_, int N_) {
+    a = a_; a_bs = a_bs_; a_rs = a_rs_; nA = nA_;
+    bsrc = b_; b_bs = b_bs_; b_rs = b_rs_; nB = b_ ? nB_ : 0;
+    B = B_; N = N_;
+    stage_elems = (nA_ + nB_) * TN;                          // fixed layout even when set B is absent
+    ring = reinterpret_cast<T*>(smem);
+    size_t off = ((size_t)NSTAGE * stage_elems * sizeof(T) + 15) & ~(size_t)15;
+    bars = reinterpret_cast<uint64_t*>(smem + off);
+    pb = blockIdx.x; pn0 = 0; pst = 0; st = 0; ph = 0;
+    if (threadIdx.x == 0) {
+#pragma unroll
+      for (int s = 0; s < NSTAGE; ++s) mbar_init(&bars[s], 1);
+      mbar_fence_init();
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+#pragma unroll
+      for (int s = 0; s < NSTAGE; ++s) issue();
+    }
+  }
+  static __host__ __device__ size_t bytes(int nA_, int nB_) {   // ring + barriers, 16-byte granular
+    return (((size_t)NSTAGE * (nA_ + nB_) * TN * sizeof(T) + 15) & ~(size_t)15) + 64;
+  }
+  __device__ __forceinline__ void issue() {                  // thread 0 only, after the stage was handed back
+    if (pb >= B) return;
+    const int rows = min(TN, N - pn0);
+    const unsigned nbytes = (unsigned)rows * (unsigned)sizeof(T);
+    T* dst = ring + (size_t)pst * stage_elems;
+    uint64_t* bar = &bars[pst];
+    mbar_expect_tx(bar, nbytes * (unsigned)(nA + nB));
+    const T* src = a + pb * a_bs + pn0;
+    for (int r = 0; r < nA; ++r, src += a_rs, dst += TN) bulk_g2s(dst, src, nbytes, bar);
+    if (nB) {
+      const T* s2 = bsrc + pb * b_bs + pn0;
+      for (int r = 0; r < nB; ++r, s2 += b_rs, dst += TN) bulk_g2s(dst, s2, nbytes, bar);
+    }
+    pn0 += TN;
+    if (pn0 >= N) { pn0 = 0; pb += gridDim.x; }
+    pst = (pst + 1 == NSTAGE) ? 0 : pst + 1;
+  }
+  __device__ __forceinline__ const T* wait() {               // all threads; returns the stage base
+    mbar_wait(&bars[st], ph);
+    return ring + (size_t)st * stage_elems;
+  }
+  __device__ __forceinline__ void advance() { if (++st == NSTAGE) { st = 0; ph ^= 1u; } }
+};
+
 // ------------------------------------------------------------------ fused normal equations, bulk-copy staged
 // Same arithmetic as k_model_normal_eq, but the data rows y[b,c,n0:n0+TN] and f_prev[b,c,n0:n0+TN]
 // of a tile are brought into shared memory by 1-D bulk async copies (cp.async.bulk -> UBLKCP,
@@ -430,6 +493,168 @@ k_model_cost_stat(const T* __restrict__ p, const T* __restrict__ x, const T* __r
   }
 }
 
+// ------------------------------------------------------------------ fused trial cost, bulk-copy staged
+template <typename T, typename Model, int TPB, int S, int NSTAGE>
+__global__ void __launch_bounds__(TPB)
+k_model_cost_stat_staged(const T* __restrict__ p, const T* __restrict__ x, const T* __restrict__ y, long long ybs,
+                         long long ycs, long long B, int C, int N, double* __restrict__ out, const nlls_ctrl* ctrl) {
+  if (is_done(ctrl)) return;
+  constexpr int P = Model::P, NW = TPB / 32, TN = TPB * S;
+  const int Cy = (ycs == 0) ? 1 : C;
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  using Ring = TileRing<T, TN, NSTAGE>;
+  double* sfc = reinterpret_cast<double*>(smem_raw + Ring::bytes(Cy, 0));    // [2][C][TPB]
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  Ring R;
+  R.init(smem_raw, y, ybs, ycs, Cy, nullptr, 0, 0, 0, B, N);
+  int pbuf = 0;
+  for (long long b = blockIdx.x; b < B; b += gridDim.x, pbuf ^= 1) {
+    Model M;
+    M.load(p + b * P);
+    if (tid == 0 && b + gridDim.x < B) prefetch_l1(p + (b + gridDim.x) * P);
+    double* my_sfc = sfc + (size_t)pbuf * C * TPB + tid;
+    for (int c = 0; c < C; ++c) my_sfc[c * TPB] = 0.0;
+    for (int n0 = 0; n0 < N; n0 += TN) {
+      T m[S];
+#pragma unroll
+      for (int i = 0; i < S; ++i) m[i] = M.value(ld_cached(x + min(n0 + i * TPB + tid, N - 1)));
+      const T* yc = R.wait() + tid;
+      const int ystep = (Cy == 1) ? 0 : TN;
+      for (int c = 0; c < C; ++c, yc += ystep) {
+        double sfl = 0.0;
+#pragma unroll
+        for (int i = 0; i < S; ++i)
+          if (n0 + i * TPB + tid < N) { const T r = yc[i * TPB] - m[i]; sfl += (double)(r * r); }
+        my_sfc[c * TPB] += sfl;
+      }
+      if (n0 + TN < N) {
+        __syncthreads();
+        if (tid == 0) R.issue();
+      }
+      R.advance();
+    }
+    __syncthreads();
+    if (tid == 0) R.issue();
+    if (warp == NW - 1) {
+      const double* col = sfc + (size_t)pbuf * C * TPB;
+      double tot = 0.0;
+      for (int c = 0; c < C; ++c) {
+        double s = 0.0;
+#pragma unroll
+        for (int kk = 0; kk < NW; ++kk) s += col[c * TPB + kk * 32 + lane];
+        s = warp_sum(s);
+        tot = fma(s, s, tot);
+      }
+      if (lane == 0) out[b] = tot;
+    }
+  }
+}
+
+// ------------------------------------------------------------------ fused GD flavour, bulk-copy staged
+template <typename T, typename Model, int TPB, int S, int NSTAGE>
+__global__ void __launch_bounds__(TPB)
+k_model_normal_eq_gda_staged(const T* __restrict__ p, const T* __restrict__ x, const T* __restrict__ y, long long ybs,
+                             long long ycs, const T* __restrict__ w, int wlen, long long B, int C, int N, T* fsA, T* fsB,
+                             double* __restrict__ g64, double* __restrict__ H64, double* __restrict__ stats,
+                             const nlls_ctrl* ctrl) {
+  if (is_done(ctrl)) return;
+  constexpr int P = Model::P, NW = TPB / 32, NH = Tri<P>::N, V = P + NH + 2, TN = TPB * S;
+  constexpr int VP = Pow2Ceil<V>::value, OWN = 32 / VP;
+  static_assert(V <= 32, "model with too many parameters for the transposed reduction");
+  const int it = iter_index(ctrl);
+  T* __restrict__ fs_out = (it & 1) ? fsB : fsA;
+  const T* __restrict__ fs_prev = (it > 0 && fsA) ? ((it & 1) ? fsA : fsB) : nullptr;
+  const bool has_prev = fs_prev != nullptr;
+  const int Cy = (ycs == 0) ? 1 : C;
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  using Ring = TileRing<T, TN, NSTAGE>;
+  double* red = reinterpret_cast<double*>(smem_raw + Ring::bytes(Cy, 1));    // [2][NW][VP]
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  Ring R;
+  R.init(smem_raw, y, ybs, ycs, Cy, fs_prev, N, 0, 1, B, N);
+  int pbuf = 0;
+  for (long long b = blockIdx.x; b < B; b += gridDim.x, pbuf ^= 1) {
+    Model M;
+    M.load(p + b * P);
+    if (tid == 0 && b + gridDim.x < B) prefetch_l1(p + (b + gridDim.x) * P);
+    RowAcc<double, P> acc;
+    acc.clear();
+    double sd = 0.0, sq = 0.0;
+    for (int n0 = 0; n0 < N; n0 += TN) {
+      T m[S], k[S][P];
+#pragma unroll
+      for (int i = 0; i < S; ++i) M.eval(ld_cached(x + min(n0 + i * TPB + tid, N - 1)), m[i], k[i]);
+      const T* sy = R.wait() + tid;
+      const T* sp = sy + Cy * TN;
+      const int ystep = (Cy == 1) ? 0 : TN;
+      T s1[S], fs[S];
+#pragma unroll
+      for (int i = 0; i < S; ++i) { s1[i] = T(0); fs[i] = T(0); }
+      const T* yc = sy;
+      for (int c = 0; c < C; ++c, yc += ystep) {
+        const T wc = w[wlen == 1 ? 0 : c];
+#pragma unroll
+        for (int i = 0; i < S; ++i) {
+          const T r = yc[i * TPB] - m[i];                    // rows past N hold stale data; masked below
+          s1[i] = fma(wc, r, s1[i]);
+          fs[i] = fma(wc, r * r, fs[i]);                     // gda:136
+        }
+      }
+#pragma unroll
+      for (int i = 0; i < S; ++i) {
+        const int n = n0 + i * TPB + tid;
+        if (n < N) {
+          double jd[P];
+#pragma unroll
+          for (int q = 0; q < P; ++q) jd[q] = (double)(T(2) * s1[i] * k[i][q]);   // gda:137 (cost-summed row, in T)
+          acc.add(jd, (double)fs[i], 1.0);
+          if (fs_out) fs_out[b * N + n] = fs[i];
+          sq = fma((double)fs[i], (double)fs[i], sq);
+          if (has_prev) { const T d = sp[i * TPB] - fs[i]; sd = fma((double)d, (double)d, sd); }
+        }
+      }
+      if (n0 + TN < N) {
+        __syncthreads();
+        if (tid == 0) R.issue();
+      }
+      R.advance();
+    }
+    double v[VP];
+#pragma unroll
+    for (int i = 0; i < P; ++i) v[i] = acc.g[i];
+#pragma unroll
+    for (int i = 0; i < NH; ++i) v[P + i] = acc.h[i];
+    v[P + NH] = sd;
+    v[P + NH + 1] = sq;
+#pragma unroll
+    for (int i = V; i < VP; ++i) v[i] = 0.0;
+    warp_reduce_transpose<VP>(v);
+    double* myred = red + (size_t)pbuf * NW * VP;
+    if ((lane & (OWN - 1)) == 0) myred[warp * VP + lane / OWN] = v[0];
+    __syncthreads();
+    if (tid == 0) R.issue();
+    if (tid < V) {
+      double s = 0.0;
+#pragma unroll
+      for (int kk = 0; kk < NW; ++kk) s += myred[kk * VP + tid];
+      if (tid < P) {
+        g64[b * P + tid] = s;
+      } else if (tid < P + NH) {
+        int kk = tid - P, i = 0;
+        while (kk >= P - i) { kk -= P - i; ++i; }
+        const int j = i + kk;
+        H64[b * P * P + i * P + j] = s;
+        H64[b * P * P + j * P + i] = s;
+      } else {
+        stats[b * 4 + (tid - P - NH) + 1] = s;
+      }
+    } else if (tid == V) {
+      stats[b * 4 + 0] = 0.0;
+      stats[b * 4 + 3] = 0.0;
+    }
+  }
+}
+
 // ------------------------------------------------------------------ materialising callables
 // thread per (b, n): writes f[b,c,n] and J[b,c,n,:] for every cost c.
 template <typename T, typename Model>
@@ -523,6 +748,52 @@ static int launch_staged(const ModelArgs& a) {
 }
 
 
+template <typename T>
+static bool rows16(const ModelArgs& a) {
+  const size_t es = sizeof(T);
+  return aligned_to(a.y, 16) && (a.ybs * es) % 16 == 0 && (a.ycs * es) % 16 == 0 && ((size_t)a.N * es) % 16 == 0;
+}
+
+template <typename T, typename Model, int TPB2, int S2>
+static int launch_cost_staged(const ModelArgs& a) {
+  constexpr int TN = TPB2 * S2;
+  if (!rows16<T>(a)) return 1;
+  const int Cy = a.ycs == 0 ? 1 : a.C;
+  const size_t tail = (size_t)2 * a.C * TPB2 * 8;
+  const int want_ctas = 1024 / TPB2;                         // cost-only evaluation: ~64 registers per thread
+  const bool three = (size_t)want_ctas * (TileRing<T, TN, 3>::bytes(Cy, 0) + tail + 1024) <= 226 * 1024;
+  const size_t smem2 = (three ? TileRing<T, TN, 3>::bytes(Cy, 0) : TileRing<T, TN, 2>::bytes(Cy, 0)) + tail;
+  if (smem2 > 220 * 1024) return 1;
+  auto launch = [&](auto kern2) {
+    const int grid2 = grid_for(kern2, TPB2, smem2, a.B);
+    kern2<<<grid2, TPB2, smem2, a.st>>>((const T*)a.p, (const T*)a.x, (const T*)a.y, a.ybs, a.ycs, a.B, a.C, a.N, a.stat_out,
+                                        a.ctrl);
+  };
+  if (three) launch(k_model_cost_stat_staged<T, Model, TPB2, S2, 3>);
+  else launch(k_model_cost_stat_staged<T, Model, TPB2, S2, 2>);
+  return check_launch("nlls_model_cost_stat(staged)");
+}
+
+template <typename T, typename Model, int TPB2, int S2>
+static int launch_gda_staged(const ModelArgs& a) {
+  constexpr int P = Model::P, V = P + Tri<P>::N + 2, NW2 = TPB2 / 32, TN = TPB2 * S2, VP = Pow2Ceil<V>::value;
+  if (!rows16<T>(a) || (a.fA && !(aligned_to(a.fA, 16) && aligned_to(a.fB, 16)))) return 1;
+  const int Cy = a.ycs == 0 ? 1 : a.C;
+  const size_t tail = (size_t)2 * NW2 * VP * 8;
+  const int want_ctas = 512 / TPB2;
+  const bool three = (size_t)want_ctas * (TileRing<T, TN, 3>::bytes(Cy, 1) + tail + 1024) <= 226 * 1024;
+  const size_t smem2 = (three ? TileRing<T, TN, 3>::bytes(Cy, 1) : TileRing<T, TN, 2>::bytes(Cy, 1)) + tail;
+  if (smem2 > 220 * 1024) return 1;
+  auto launch = [&](auto kern2) {
+    const int grid2 = grid_for(kern2, TPB2, smem2, a.B);
+    kern2<<<grid2, TPB2, smem2, a.st>>>((const T*)a.p, (const T*)a.x, (const T*)a.y, a.ybs, a.ycs, (const T*)a.w, a.wlen, a.B,
+                                        a.C, a.N, (T*)a.fA, (T*)a.fB, a.g64, a.H64, a.stats, a.ctrl);
+  };
+  if (three) launch(k_model_normal_eq_gda_staged<T, Model, TPB2, S2, 3>);
+  else launch(k_model_normal_eq_gda_staged<T, Model, TPB2, S2, 2>);
+  return check_launch("nlls_model_normal_eq_gda(staged)");
+}
+
 template <typename T, typename Model>
 static int run_op(Op op, const ModelArgs& a) {
   constexpr int TPB = kFusedTPB, S = kFusedS, NW = TPB / 32, P = Model::P, V = P + Tri<P>::N + 2;
@@ -547,6 +818,10 @@ static int run_op(Op op, const ModelArgs& a) {
       return check_launch("nlls_model_normal_eq");
     }
     case OP_NEQ_GDA: {
+      if (!g_force_direct) {
+        const int rc = launch_gda_staged<T, Model, 128, 2>(a);
+        if (rc <= 0) return rc;
+      }
       auto kern = k_model_normal_eq_gda<T, Model, TPB>;
       const int grid = grid_for(kern, TPB, 0, a.B);
       kern<<<grid, TPB, 0, a.st>>>((const T*)a.p, (const T*)a.x, (const T*)a.y, a.ybs, a.ycs, (const T*)a.w, a.wlen, a.B, a.C,
@@ -556,6 +831,10 @@ static int run_op(Op op, const ModelArgs& a) {
     case OP_COST: {
       const size_t smem = ((size_t)a.C * TPB + (size_t)a.C * NW) * 8;
       if (smem > 200 * 1024) { set_error("fused model path: too many costs (C=%d)", a.C); return NLLS_E_SHAPE; }
+      if (!g_force_direct) {
+        const int rc = launch_cost_staged<T, Model, 128, 2>(a);
+        if (rc <= 0) return rc;
+      }
       auto kern = k_model_cost_stat<T, Model, TPB, S>;
       const int grid = grid_for(kern, TPB, smem, a.B);
       kern<<<grid, TPB, smem, a.st>>>((const T*)a.p, (const T*)a.x, (const T*)a.y, a.ybs, a.ycs, a.B, a.C, a.N, a.stat_out,
