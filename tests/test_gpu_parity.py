@@ -61,6 +61,7 @@ K1_SHAPES = [  # B, C, N, P
     (7, 2, 2000, 4), (5, 5, 1024, 4), (9, 1, 1000, 5), (3, 3, 130, 3), (4, 2, 257, 4), (6, 1, 64, 1),
     (3, 2, 96, 2), (5, 1, 512, 6), (4, 2, 300, 7), (3, 1, 1024, 8), (300, 1, 40, 4), (3, 1, 4096, 16),
     (2, 2, 200, 12), (2, 1, 100, 9), (2, 1, 128, 24), (1, 1, 7, 4), (2, 70, 16, 4),
+    (2, 3, 333, 17), (2, 2, 250, 32), (3, 1, 1023, 16), (2, 2, 5, 10),
 ]
 
 
@@ -100,7 +101,7 @@ def test_normal_eq_without_f_prev_and_broadcast_weight():
 
 
 @pytest.mark.parametrize('dn', ['f64', 'f32'])
-@pytest.mark.parametrize('shape', [(6, 2, 500, 4), (4, 3, 1000, 5), (3, 1, 77, 3), (2, 2, 64, 12)])
+@pytest.mark.parametrize('shape', [(6, 2, 500, 4), (4, 3, 1000, 5), (3, 1, 77, 3), (2, 2, 64, 12), (2, 3, 301, 16), (2, 1, 90, 25)])
 def test_normal_eq_gda_matches_oracle(shape, dn):
     dt = DT[dn]
     B, C, N, P = shape

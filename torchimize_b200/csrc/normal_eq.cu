@@ -377,6 +377,194 @@ k_normal_eq_wide(const T* __restrict__ J, const T* __restrict__ f, const T* __re
   }
 }
 
+// ============================================================================== DMMA (8 < P <= 32)
+// fp64 tensor-core path for wide rows.  H = sum_n J_n^T J_n is a (P x rows) x (rows x P) product, so
+// it maps onto mma.sync.m8n8k4.f64 (SASS DMMA) with K = 4 residual rows per instruction: lane
+// (gi = lane >> 2, k = lane & 3) holds J[n0 + k][8 I + gi] for every 8-column block I, and that ONE
+// register is both the A fragment of block-row I (A[gi][k] = J^T) and the B fragment of block-column
+// I (B[k][gi] = J).  Per 4 rows a warp issues NB coalesced 8-byte loads (each touching 4 x 64
+// contiguous bytes), NB (NB + 1) / 2 DMMAs for the upper block triangle and NB DFMAs for g —
+// about 3 warp instructions per row at P = 16 instead of the ~80 of the lane-split FMA kernel,
+// which was bound by its redundant row loads (profiles/r01d_cfg4.txt).  fp32 inputs are widened on
+// load; products and sums are fp64 (at least as accurate as the reference's fp32 bmm).
+// GDA = true: rows are first summed over the costs in T (gda:136-137), outputs are the fp64 normal
+// equations of the tall system, f_s is written out.
+__device__ __forceinline__ void dmma_884(double& d0, double& d1, double a, double b) {
+  asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
+               : "+d"(d0), "+d"(d1) : "d"(a), "d"(b));
+}
+
+template <typename T, int NB, int NW, int U, bool GDA>
+__global__ void __launch_bounds__(NW * 32, NB == 2 ? 3 : (NB == 3 ? 2 : 1))
+k_normal_eq_dmma(const T* __restrict__ J, const T* __restrict__ f, const T* __restrict__ fprev,
+                 const T* __restrict__ w, int wlen, long long B, int C, int N, int P,
+                 void* __restrict__ gout, void* __restrict__ Hout, T* __restrict__ fsum_out,
+                 double* __restrict__ stats, const nlls_ctrl* ctrl) {
+  if (is_done(ctrl)) return;
+  constexpr int NBT = NB * (NB + 1) / 2, RW = NBT * 64 + NB * 8 + 2, TPB = NW * 32;
+  extern __shared__ double smem[];
+  double* red = smem;                    // [NW][RW]: block triangle of H, g, {sd, sq}
+  double* sfc = smem + NW * RW;          // [C][NW] per-cost sums of f (unused for GDA)
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int k = lane & 3, gi = lane >> 2;
+  const int G = (N + 3) >> 2;            // 4-row groups per (b,c) segment
+  bool colok[NB];
+#pragma unroll
+  for (int I = 0; I < NB; ++I) colok[I] = 8 * I + gi < P;
+
+  for (long long b = blockIdx.x; b < B; b += gridDim.x) {
+    double Ht[NBT][2], Gt[NB];
+#pragma unroll
+    for (int i = 0; i < NBT; ++i) Ht[i][0] = Ht[i][1] = 0.0;
+#pragma unroll
+    for (int I = 0; I < NB; ++I) Gt[I] = 0.0;
+    double sd = 0.0, sq = 0.0;
+    if constexpr (!GDA) {
+      for (int c = 0; c < C; ++c) {
+        const long long seg = (b * C + c) * (long long)N;
+        const T* Jc = J + seg * P + gi;
+        const T* fc = f + seg;
+        const T* pc = fprev ? fprev + seg : nullptr;
+        double Hc[NBT][2], Gc[NB], sf = 0.0;
+#pragma unroll
+        for (int i = 0; i < NBT; ++i) Hc[i][0] = Hc[i][1] = 0.0;
+#pragma unroll
+        for (int I = 0; I < NB; ++I) Gc[I] = 0.0;
+        for (int g0 = warp; g0 < G; g0 += NW * U) {
+          T v[U][NB], fv[U], pv[U];
+#pragma unroll
+          for (int u = 0; u < U; ++u) {
+            const int n = 4 * (g0 + u * NW) + k;
+            const bool ok = n < N;
+#pragma unroll
+            for (int I = 0; I < NB; ++I) v[u][I] = (ok && colok[I]) ? ldg_stream(Jc + (long long)n * P + 8 * I) : T(0);
+            fv[u] = ok ? ldg_stream(fc + n) : T(0);
+            pv[u] = (ok && pc && gi == 0) ? ldg_stream(pc + n) : fv[u];
+          }
+#pragma unroll
+          for (int u = 0; u < U; ++u) {
+            double vd[NB];
+#pragma unroll
+            for (int I = 0; I < NB; ++I) vd[I] = (double)v[u][I];
+            int idx = 0;
+#pragma unroll
+            for (int I = 0; I < NB; ++I)
+#pragma unroll
+              for (int Jb = I; Jb < NB; ++Jb, ++idx) dmma_884(Hc[idx][0], Hc[idx][1], vd[I], vd[Jb]);
+            const double fd = (double)fv[u];
+#pragma unroll
+            for (int I = 0; I < NB; ++I) Gc[I] = fma(vd[I], fd, Gc[I]);
+            if (gi == 0) {
+              sf += fd;
+              sq = fma(fd, fd, sq);
+              const double d = (double)(T)(pv[u] - fv[u]);
+              sd = fma(d, d, sd);
+            }
+          }
+        }
+        const double wc = (double)w[wlen == 1 ? 0 : c];
+#pragma unroll
+        for (int i = 0; i < NBT; ++i) { Ht[i][0] = fma(wc, Hc[i][0], Ht[i][0]); Ht[i][1] = fma(wc, Hc[i][1], Ht[i][1]); }
+#pragma unroll
+        for (int I = 0; I < NB; ++I) Gt[I] = fma(wc, Gc[I], Gt[I]);
+        sf = warp_sum(sf);
+        if (lane == 0) sfc[c * NW + warp] = sf;
+      }
+    } else {
+      const T* fsp = fprev ? fprev + b * (long long)N : nullptr;   // fsum_prev [B,N]
+      for (int g0 = warp; g0 < G; g0 += NW * U) {
+        T js[U][NB], fs[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+          fs[u] = T(0);
+#pragma unroll
+          for (int I = 0; I < NB; ++I) js[u][I] = T(0);
+        }
+        for (int c = 0; c < C; ++c) {
+          const T wc = w[wlen == 1 ? 0 : c];
+          const long long seg = (b * C + c) * (long long)N;
+#pragma unroll
+          for (int u = 0; u < U; ++u) {
+            const int n = 4 * (g0 + u * NW) + k;
+            if (n < N) {
+#pragma unroll
+              for (int I = 0; I < NB; ++I)
+                if (colok[I]) js[u][I] = fma(ldg_stream(J + (seg + n) * P + 8 * I + gi), wc, js[u][I]);
+              fs[u] = fma(ldg_stream(f + seg + n), wc, fs[u]);
+            }
+          }
+        }
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+          const int n = 4 * (g0 + u * NW) + k;
+          double vd[NB];
+#pragma unroll
+          for (int I = 0; I < NB; ++I) vd[I] = (double)js[u][I];
+          int idx = 0;
+#pragma unroll
+          for (int I = 0; I < NB; ++I)
+#pragma unroll
+            for (int Jb = I; Jb < NB; ++Jb, ++idx) dmma_884(Ht[idx][0], Ht[idx][1], vd[I], vd[Jb]);
+          const double fd = (double)fs[u];
+#pragma unroll
+          for (int I = 0; I < NB; ++I) Gt[I] = fma(vd[I], fd, Gt[I]);
+          if (gi == 0 && n < N) {
+            if (fsum_out) fsum_out[b * N + n] = fs[u];
+            sq = fma(fd, fd, sq);
+            if (fsp) { const double d = (double)(T)(fsp[n] - fs[u]); sd = fma(d, d, sd); }
+          }
+        }
+      }
+    }
+    // ---- warp partials -> shared memory
+#pragma unroll
+    for (int I = 0; I < NB; ++I) { Gt[I] += shfl_xor(Gt[I], 1); Gt[I] += shfl_xor(Gt[I], 2); }
+    sd = warp_sum(sd);
+    sq = warp_sum(sq);
+    double* r = red + warp * RW;
+#pragma unroll
+    for (int i = 0; i < NBT; ++i) { r[i * 64 + gi * 8 + 2 * k] = Ht[i][0]; r[i * 64 + gi * 8 + 2 * k + 1] = Ht[i][1]; }
+    if (k == 0) {
+#pragma unroll
+      for (int I = 0; I < NB; ++I) r[NBT * 64 + I * 8 + gi] = Gt[I];
+    }
+    if (lane == 0) { r[NBT * 64 + NB * 8] = sd; r[NBT * 64 + NB * 8 + 1] = sq; }
+    __syncthreads();
+    for (int e = tid; e < P * P; e += TPB) {
+      const int i = e / P, j = e - i * P;
+      const int lo = min(i, j), hi = max(i, j);
+      const int I = lo >> 3, Jb = hi >> 3;
+      const int off = (I * NB - (I * (I - 1)) / 2 + (Jb - I)) * 64 + (lo & 7) * 8 + (hi & 7);
+      double s = 0.0;
+#pragma unroll
+      for (int ww = 0; ww < NW; ++ww) s += red[ww * RW + off];
+      if constexpr (GDA) reinterpret_cast<double*>(Hout)[b * P * P + e] = s;
+      else reinterpret_cast<T*>(Hout)[b * P * P + e] = (T)s;
+    }
+    if (tid < P) {
+      double s = 0.0;
+#pragma unroll
+      for (int ww = 0; ww < NW; ++ww) s += red[ww * RW + NBT * 64 + tid];
+      if constexpr (GDA) reinterpret_cast<double*>(gout)[b * P + tid] = s;
+      else reinterpret_cast<T*>(gout)[b * P + tid] = (T)s;
+    }
+    if (tid == TPB - 1) {
+      double s1 = 0.0, s2 = 0.0, tot = 0.0;
+#pragma unroll
+      for (int ww = 0; ww < NW; ++ww) { s1 += red[ww * RW + NBT * 64 + NB * 8]; s2 += red[ww * RW + NBT * 64 + NB * 8 + 1]; }
+      if constexpr (!GDA) {
+        for (int c = 0; c < C; ++c) {
+          double s = 0.0;
+          for (int ww = 0; ww < NW; ++ww) s += sfc[c * NW + ww];
+          tot = fma(s, s, tot);
+        }
+      }
+      stats[b * 4 + 0] = tot; stats[b * 4 + 1] = s1; stats[b * 4 + 2] = s2; stats[b * 4 + 3] = 0.0;
+    }
+    __syncthreads();
+  }
+}
+
 // ======================================================================= cost statistic
 // stat[b] = sum_c (sum_n f[b,c,n])^2  (lma:100).  One warp per (b), lanes stride n.
 template <typename T>
@@ -604,6 +792,20 @@ static int launch_normal_eq(const void* J, const void* f, const void* fprev, con
     default: break;
   }
 #undef NLLS_CASE
+  if (!g_force_direct) {
+    constexpr int NWD = 8;
+    const int NB = (P + 7) / 8;
+    const size_t smemd = ((size_t)NWD * (NB * (NB + 1) / 2 * 64 + NB * 8 + 2) + (size_t)C * NWD) * 8;
+    auto go = [&](auto kern) {
+      const int grid = occupancy_grid(kern, NWD * 32, smemd, B);
+      kern<<<grid, NWD * 32, smemd, st>>>((const T*)J, (const T*)f, (const T*)fprev, (const T*)w, wlen, B, C, N, P, g, H,
+                                          (T*)nullptr, stats, ctrl);
+    };
+    if (NB == 2) go(k_normal_eq_dmma<T, 2, NWD, 4, false>);
+    else if (NB == 3) go(k_normal_eq_dmma<T, 3, NWD, 2, false>);
+    else go(k_normal_eq_dmma<T, 4, NWD, 2, false>);
+    return check_launch("nlls_normal_eq(dmma)");
+  }
   constexpr int TPB = 128, NW = TPB / 32;
   if (P <= 16) {
     constexpr int PP = 16;
@@ -644,6 +846,20 @@ static int launch_normal_eq_gda(const void* J, const void* f, const void* fsp, c
     default: break;
   }
 #undef NLLS_CASE
+  if (!g_force_direct) {
+    constexpr int NWD = 8;
+    const int NB = (P + 7) / 8;
+    const size_t smemd = ((size_t)NWD * (NB * (NB + 1) / 2 * 64 + NB * 8 + 2)) * 8;
+    auto go = [&](auto kern) {
+      const int grid = occupancy_grid(kern, NWD * 32, smemd, B);
+      kern<<<grid, NWD * 32, smemd, st>>>((const T*)J, (const T*)f, (const T*)fsp, (const T*)w, wlen, B, C, N, P, g64, H64,
+                                          (T*)fso, stats, ctrl);
+    };
+    if (NB == 2) go(k_normal_eq_dmma<T, 2, NWD, 4, true>);
+    else if (NB == 3) go(k_normal_eq_dmma<T, 3, NWD, 2, true>);
+    else go(k_normal_eq_dmma<T, 4, NWD, 2, true>);
+    return check_launch("nlls_normal_eq_gda(dmma)");
+  }
   constexpr int WT = 256, TILE = 64;
   const size_t smem = ((size_t)TILE * (P + 1) + WT) * 8;
   auto kern = k_normal_eq_gda_wide<T, WT, TILE>;

@@ -6,6 +6,7 @@
 // microseconds at B = 65536; what they buy is the removal of the reference's ~100 small
 // launches and ~20 host synchronisations per iteration (boolean-mask indexing at
 // lma:103,105,115,131-134; `converged.all()` at lma:118) — every decision stays on the device.
+#include <type_traits>
 #include "common.cuh"
 
 namespace nlls {
@@ -297,6 +298,225 @@ __global__ void k_iter_end(nlls_ctrl* ctrl, int solver, double ftol) {
   ctrl->red[0] = ctrl->red[1] = ctrl->red[2] = ctrl->red[3] = 0.0;
 }
 
+// =========================================================== warp-cooperative solve, 8 < P <= 32
+// One warp per problem, lane i owns row i of the (damped) matrix in REGISTERS.  Left-looking
+// Cholesky with fully unrolled static register indices; L[j][k] reaches the other lanes by a
+// register shuffle, so the factorisation touches no memory: P(P-1)/2 x (2 SHFL + DFMA) plus one
+// sqrt and one reciprocal per column.  Forward substitution is column-oriented on registers; the
+// transposed access of the back substitution goes through a per-warp shared-memory copy of L
+// (leading dimension PP + 1: conflict-free for both the row writes and the column reads).
+// The r01d profile of the thread-per-problem kernel it replaces showed one resident warp per SM
+// (139 KB of interleaved scratch per 32 problems): profiles/r01d_cfg4.txt.
+// A non-positive / non-finite pivot sends the ORIGINAL matrix (kept in shared memory) through LU
+// with partial pivoting on lane 0 (rare path: Marquardt overflow, singular Hessians).
+__device__ inline bool lu_solve_rt(int P, double* M, int ld, double* b, double* x) {
+  const double INF = __longlong_as_double(0x7ff0000000000000LL);
+  bool nonsing = true;
+  for (int k = 0; k < P; ++k) {
+    int piv = k;
+    double best = fabs(M[k * ld + k]);
+    for (int i = k + 1; i < P; ++i) {
+      const double a = fabs(M[i * ld + k]);
+      if (a > best) { best = a; piv = i; }
+    }
+    if (piv != k) {
+      for (int j = 0; j < P; ++j) { const double t = M[k * ld + j]; M[k * ld + j] = M[piv * ld + j]; M[piv * ld + j] = t; }
+      const double t = b[k]; b[k] = b[piv]; b[piv] = t;
+    }
+    const double d = M[k * ld + k];
+    nonsing = nonsing && (d != 0.0) && (fabs(d) < INF);
+    const double inv = 1.0 / d;
+    for (int i = k + 1; i < P; ++i) {
+      const double m = M[i * ld + k] * inv;
+      for (int j = k + 1; j < P; ++j) M[i * ld + j] -= m * M[k * ld + j];
+      b[i] -= m * b[k];
+    }
+  }
+  for (int i = P - 1; i >= 0; --i) {
+    double sacc = b[i];
+    for (int k = i + 1; k < P; ++k) sacc -= M[i * ld + k] * x[k];
+    x[i] = sacc / M[i * ld + i];
+  }
+  return nonsing;
+}
+
+template <int PP>
+__device__ __forceinline__ bool warp_chol_solve(double (&row)[PP], double rhs, double* Ls, int lane, double& x_out) {
+  constexpr unsigned FULL = 0xffffffffu;
+  constexpr int LD = PP + 1;
+  const double INF = __longlong_as_double(0x7ff0000000000000LL);
+  bool ok = true;
+  double myinv = 1.0;
+#pragma unroll
+  for (int j = 0; j < PP; ++j) {
+    double sacc = row[j];
+#pragma unroll
+    for (int k = 0; k < j; ++k) sacc = fma(-row[k], __shfl_sync(FULL, row[k], j), sacc);
+    const double d = __shfl_sync(FULL, sacc, j);
+    ok = ok && (d > 0.0) && (d < INF);
+    const double dj = sqrt(d);
+    const double inv = 1.0 / dj;
+    if (lane == j) myinv = inv;
+    row[j] = (lane == j) ? dj : sacc * inv;       // lanes < j: upper-triangle slot, never read
+  }
+  if (!ok) return false;                          // warp-uniform
+  if (lane < PP) {
+#pragma unroll
+    for (int j = 0; j < PP; ++j) Ls[lane * LD + j] = row[j];
+  }
+  double bb = rhs;                                // L y = b
+#pragma unroll
+  for (int k = 0; k < PP; ++k) {
+    if (lane == k) bb *= myinv;
+    const double yk = __shfl_sync(FULL, bb, k);
+    if (lane > k) bb = fma(-row[k], yk, bb);
+  }
+  __syncwarp();
+#pragma unroll
+  for (int k = PP - 1; k >= 0; --k) {             // L^T x = y
+    if (lane == k) bb *= myinv;
+    const double xk = __shfl_sync(FULL, bb, k);
+    if (lane < k) bb = fma(-Ls[k * LD + lane], xk, bb);
+  }
+  __syncwarp();
+  x_out = bb;
+  return true;
+}
+
+enum { W_LM = 0, W_GN = 1, W_GD = 2 };
+struct WideArgs {
+  const void *g, *H, *u;
+  void *p, *dscale, *h, *p_trial, *h_out, *p_hist;
+  const double* stats;
+  double l, ftol, ptol, gtol;
+  long long B;
+  int P, marquardt, with_masks;
+  nlls_ctrl* ctrl;
+};
+constexpr int kWideWarps = 4;
+template <int PP> constexpr size_t wide_smem_bytes() { return (size_t)kWideWarps * (2 * PP * (PP + 1) + 2 * PP) * 8; }
+
+template <typename T> __device__ __forceinline__ T warp_nan_max(T v) {
+#pragma unroll
+  for (int m = 16; m > 0; m >>= 1) v = nan_max(v, shfl_xor(v, m));
+  return v;
+}
+
+template <typename T, int PP, int MODE>
+__global__ void __launch_bounds__(kWideWarps * 32) k_solve_wide(WideArgs a) {
+  if (is_done(a.ctrl)) return;
+  using TH = typename std::conditional<MODE == W_GD, double, T>::type;
+  constexpr int LD = PP + 1;
+  extern __shared__ double sm[];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  double* M = sm + (size_t)warp * (2 * PP * LD + 2 * PP);
+  double* Ls = M + PP * LD;
+  double* bs = Ls + PP * LD;
+  double* xs = bs + PP;
+  const int it = iter_index(a.ctrl);
+  const int P = a.P;
+  const bool act = lane < P;
+  T* p = reinterpret_cast<T*>(a.p);
+  int nc = 0, sing = 0;
+  for (long long b = (long long)blockIdx.x * kWideWarps + warp; b < a.B; b += (long long)gridDim.x * kWideWarps) {
+    const TH* Hb = reinterpret_cast<const TH*>(a.H) + b * P * P;
+    T diag_add = T(0), off_add = T(0);
+    if constexpr (MODE == W_LM) {
+      T* ds = reinterpret_cast<T*>(a.dscale);
+      T dd = ds[b * 2], doff = ds[b * 2 + 1];
+      if (a.marquardt) {                             // lma:88 — D <- D * max_p max(H_pp, D_pp)   (Q6)
+        T m = act ? nan_max((T)Hb[lane * P + lane], dd) : dd;
+        m = warp_nan_max(m);
+        dd = dd * m;
+        doff = doff * m;
+        __syncwarp();
+        if (lane == 0) { ds[b * 2] = dd; ds[b * 2 + 1] = doff; }
+      }
+      const T ub = reinterpret_cast<const T*>(a.u)[b];
+      diag_add = ub * dd;
+      off_add = ub * doff;
+    }
+    double row[PP];
+#pragma unroll
+    for (int j = 0; j < PP; ++j) {
+      double v = (lane == j) ? 1.0 : 0.0;            // identity padding keeps the factorisation well defined
+      if (act && j < P) {
+        TH hv = Hb[j * P + lane];                    // H is symmetric: column read = coalesced row read
+        if constexpr (MODE == W_LM) hv = (TH)((T)hv + (lane == j ? diag_add : off_add));   // Hu formed in T (lma:97-98)
+        v = (double)hv;
+      }
+      row[j] = v;
+      if (lane < PP) M[lane * LD + j] = v;
+    }
+    const double rhs = act ? (double)reinterpret_cast<const TH*>(a.g)[b * P + lane] : 0.0;
+    if (lane < PP) bs[lane] = rhs;
+    __syncwarp();
+    double x = 0.0;
+    bool ok = warp_chol_solve<PP>(row, rhs, Ls, lane, x);
+    if (!ok) {
+      int ns = 0;
+      if (lane == 0) ns = lu_solve_rt(P, M, LD, bs, xs) ? 1 : 0;
+      ns = __shfl_sync(0xffffffffu, ns, 0);
+      __syncwarp();
+      x = act ? xs[lane] : 0.0;
+      ok = ns != 0;
+      __syncwarp();
+    }
+    if (!ok) sing = 1;
+    if constexpr (MODE == W_LM) {
+      if (act) {
+        const T hi = -(T)x;                          // lma:98
+        reinterpret_cast<T*>(a.h)[b * P + lane] = hi;
+        reinterpret_cast<T*>(a.p_trial)[b * P + lane] = p[b * P + lane] + hi;
+      }
+    } else {
+      const T l = (T)a.l;
+      const T hb = act ? (T)x : T(0);
+      T pb = T(0), gb = T(0);
+      if (act) {
+        pb = p[b * P + lane] - l * hb;               // gna:141 / gda:146 (in place, Q1)
+        p[b * P + lane] = pb;
+        if (a.h_out) reinterpret_cast<T*>(a.h_out)[b * P + lane] = hb;
+        gb = (MODE == W_GD) ? hb / l : (T)reinterpret_cast<const TH*>(a.g)[b * P + lane];
+        if (a.p_hist) reinterpret_cast<T*>(a.p_hist)[((long long)it * a.B + b) * P + lane] = pb;
+      }
+      if (a.with_masks) {
+        T ga = fabs(gb);
+        const T ga0 = __shfl_sync(0xffffffffu, ga, 0);   // padding lanes repeat lane 0 (identity of the NaN-propagating max)
+        ga = act ? ga : ga0;
+        const T gm = warp_nan_max(ga);
+        const T hh = warp_sum(hb * hb), pp = warp_sum(pb * pb);
+        const bool gcon = gm < (T)a.gtol;
+        const bool pcon = sqrt(hh) < (T)a.ptol * ((T)a.ptol + sqrt(pp));
+        bool fcon = false;
+        if constexpr (MODE == W_GN) fcon = (it > 0) && (a.stats[b * 4 + 1] < a.ftol * a.ftol * a.stats[b * 4 + 2]);
+        nc += !(gcon || pcon || fcon);
+      }
+    }
+  }
+  if (a.ctrl && lane == 0) {
+    if (sing) a.ctrl->singular = 1;
+    if (nc) atomicAdd(&a.ctrl->red[0], (double)nc);  // integer-valued: order-independent
+  }
+}
+
+template <typename T, int MODE>
+static int launch_wide(const WideArgs& a, cudaStream_t st, const char* what) {
+  auto go = [&](auto kern, size_t smem) {
+    if (smem > 48 * 1024) cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    int per_sm = 1;
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, kWideWarps * 32, smem);
+    if (per_sm < 1) per_sm = 1;
+    long long grid = (long long)kNumSMs * per_sm;
+    const long long need = (a.B + kWideWarps - 1) / kWideWarps;
+    if (grid > need) grid = need;
+    kern<<<(int)grid, kWideWarps * 32, smem, st>>>(a);
+  };
+  if (a.P <= 16) go(k_solve_wide<T, 16, MODE>, wide_smem_bytes<16>());
+  else go(k_solve_wide<T, 32, MODE>, wide_smem_bytes<32>());
+  return check_launch(what);
+}
+
 template <typename K>
 static void allow_smem(K kern, size_t smem) {
   if (smem > 48 * 1024) cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
@@ -317,6 +537,13 @@ extern "C" int nlls_lm_solve(int dtype, const void* g, const void* H, const void
   if (int e = check_bp(dtype, B, P)) return e;
   if (B == 0) return 0;
   if (!g || !H || !p || !u || !dscale || !h || !p_trial) { set_error("nlls_lm_solve: NULL tensor"); return NLLS_E_NULL; }
+  if (P > 8 && !g_force_direct) {
+    WideArgs a{};
+    a.g = g; a.H = H; a.u = u; a.p = const_cast<void*>(p); a.dscale = dscale; a.h = h; a.p_trial = p_trial;
+    a.B = B; a.P = P; a.marquardt = marquardt; a.ctrl = ctrl;
+    return dtype == NLLS_F64 ? launch_wide<double, W_LM>(a, (cudaStream_t)stream, "nlls_lm_solve(wide)")
+                             : launch_wide<float, W_LM>(a, (cudaStream_t)stream, "nlls_lm_solve(wide)");
+  }
   const int tpb = threads_for(P);
   const size_t smem = scratch_bytes_per_thread(P) * tpb;
   const int grid = (int)((B + tpb - 1) / tpb);
@@ -359,6 +586,13 @@ extern "C" int nlls_gn_update(int dtype, void* p, const void* g, const void* H, 
   if (int e = check_bp(dtype, B, P)) return e;
   if (B == 0) return 0;
   if (!p || !g || !H || (with_masks && !stats)) { set_error("nlls_gn_update: NULL tensor"); return NLLS_E_NULL; }
+  if (P > 8 && !g_force_direct) {
+    WideArgs a{};
+    a.g = g; a.H = H; a.p = p; a.h_out = h_out; a.p_hist = p_hist; a.stats = stats; a.l = l; a.ftol = ftol; a.ptol = ptol;
+    a.gtol = gtol; a.B = B; a.P = P; a.with_masks = with_masks && ctrl; a.ctrl = ctrl;
+    return dtype == NLLS_F64 ? launch_wide<double, W_GN>(a, (cudaStream_t)stream, "nlls_gn_update(wide)")
+                             : launch_wide<float, W_GN>(a, (cudaStream_t)stream, "nlls_gn_update(wide)");
+  }
   const int tpb = threads_for(P);
   const size_t smem = scratch_bytes_per_thread(P) * tpb;
   const int grid = (int)((B + tpb - 1) / tpb);
@@ -387,7 +621,13 @@ extern "C" int nlls_gd_update(int dtype, void* p, const double* g64, const doubl
   const size_t smem = scratch_bytes_per_thread(P) * tpb;
   const int grid = (int)((B + tpb - 1) / tpb);
   cudaStream_t st = (cudaStream_t)stream;
-  if (dtype == NLLS_F64) {
+  if (P > 8 && !g_force_direct) {
+    WideArgs a{};
+    a.g = g64; a.H = H64; a.p = p; a.h_out = h_out; a.p_hist = p_hist; a.stats = stats; a.l = l; a.ftol = ftol; a.ptol = ptol;
+    a.gtol = gtol; a.B = B; a.P = P; a.with_masks = with_masks; a.ctrl = ctrl;
+    if (int e = dtype == NLLS_F64 ? launch_wide<double, W_GD>(a, st, "nlls_gd_update(wide)")
+                                  : launch_wide<float, W_GD>(a, st, "nlls_gd_update(wide)")) return e;
+  } else if (dtype == NLLS_F64) {
     allow_smem(k_gd_update<double>, smem);
     k_gd_update<double><<<grid, tpb, smem, st>>>((double*)p, g64, H64, l, ptol, gtol, with_masks, B, P, (double*)h_out,
                                                  (double*)p_hist, ctrl);
