@@ -565,6 +565,178 @@ k_normal_eq_dmma(const T* __restrict__ J, const T* __restrict__ f, const T* __re
   }
 }
 
+// ---- vector-load variant of the DMMA kernel (the one cfg-4 runs): P == 2*NB-even rows whose start
+// is NB*sizeof(T)-byte aligned.  The 8-column "blocks" of the fragment layout are INTERLEAVED:
+// block I holds the columns {NB*gi + I}, so lane (gi, k) gets its NB fragment values for row
+// n0 + k with ONE NB*sizeof(T)-byte load, and the warp's load covers 4 whole rows (4 x P x s
+// contiguous bytes).  A warp owns batches of 32 consecutive rows: 8 such loads in flight per lane,
+// f / f_prev read once per batch with one coalesced load (lane L <-> row L; the statistics are
+// then one row per lane instead of predicated on 4 lanes) and handed to the fragment layout by
+// shuffles.  r01d profile of the scalar variant: 74 instructions per 4-row step, 54 % of stalls on
+// the load scoreboard (profiles/r01d_cfg4.txt).
+template <typename T, int NB> struct VecRow;
+template <> struct VecRow<double, 2> {
+  double v[2];
+  __device__ __forceinline__ void load(const double* p) { const double2 t = ldg_stream2(p); v[0] = t.x; v[1] = t.y; }
+};
+template <> struct VecRow<double, 4> {
+  double v[4];
+  __device__ __forceinline__ void load(const double* p) {
+    asm volatile("ld.global.nc.L1::no_allocate.v4.f64 {%0,%1,%2,%3}, [%4];" : "=d"(v[0]), "=d"(v[1]), "=d"(v[2]), "=d"(v[3]) : "l"(p));
+  }
+};
+template <> struct VecRow<float, 2> {
+  float v[2];
+  __device__ __forceinline__ void load(const float* p) { const float2 t = ldg_stream2(p); v[0] = t.x; v[1] = t.y; }
+};
+template <> struct VecRow<float, 4> {
+  float v[4];
+  __device__ __forceinline__ void load(const float* p) { const float4 t = ldg_stream4(p); v[0] = t.x; v[1] = t.y; v[2] = t.z; v[3] = t.w; }
+};
+
+template <typename T, int NB, int NW>
+__global__ void __launch_bounds__(NW * 32, NB == 2 ? 2 : 1)
+k_normal_eq_dmma_vec(const T* __restrict__ J, const T* __restrict__ f, const T* __restrict__ fprev,
+                     const T* __restrict__ w, int wlen, long long B, int C, int N, int P,
+                     T* __restrict__ gout, T* __restrict__ Hout, double* __restrict__ stats, const nlls_ctrl* ctrl) {
+  if (is_done(ctrl)) return;
+  constexpr int NBT = NB * (NB + 1) / 2, PP = 8 * NB, RW = PP * PP + PP + 2, TPB = NW * 32, U = 8;
+  extern __shared__ double smem[];
+  double* red = smem;                    // [NW][RW]: H (canonical entries), g, {sd, sq}
+  double* sfc = smem + NW * RW;          // [C][NW]
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int k = lane & 3, gi = lane >> 2;
+  const bool colok = NB * gi < P;        // P is a multiple of NB: a lane's NB columns are all inside or all outside
+  const int NBATCH = (N + 31) >> 5;
+
+  for (long long b = blockIdx.x; b < B; b += gridDim.x) {
+    double Ht[NBT][2], Gt[NB];
+#pragma unroll
+    for (int i = 0; i < NBT; ++i) Ht[i][0] = Ht[i][1] = 0.0;
+#pragma unroll
+    for (int I = 0; I < NB; ++I) Gt[I] = 0.0;
+    double sd = 0.0, sq = 0.0;
+    for (int c = 0; c < C; ++c) {
+      const long long seg = (b * C + c) * (long long)N;
+      const T* Jl = J + seg * P + (long long)k * P + NB * gi;      // this lane's element of row k of a 4-row step
+      const T* fc = f + seg;
+      const T* pc = fprev ? fprev + seg : nullptr;
+      double Hc[NBT][2], Gc[NB], sf = 0.0;
+#pragma unroll
+      for (int i = 0; i < NBT; ++i) Hc[i][0] = Hc[i][1] = 0.0;
+#pragma unroll
+      for (int I = 0; I < NB; ++I) Gc[I] = 0.0;
+      for (int bt = warp; bt < NBATCH; bt += NW) {
+        const int n0 = bt << 5;
+        VecRow<T, NB> v[U];
+        T fl, pl;
+        if (n0 + 32 <= N) {                                        // full batch: no predicates
+          const T* jp = Jl + (long long)n0 * P;
+#pragma unroll
+          for (int u = 0; u < U; ++u) {
+            if (colok) v[u].load(jp + (long long)(4 * u) * P);
+            else {
+#pragma unroll
+              for (int I = 0; I < NB; ++I) v[u].v[I] = T(0);
+            }
+          }
+          fl = ldg_stream(fc + n0 + lane);
+          pl = pc ? ldg_stream(pc + n0 + lane) : fl;
+        } else {
+#pragma unroll
+          for (int u = 0; u < U; ++u) {
+            const int n = n0 + 4 * u + k;
+            if (colok && n < N) v[u].load(Jl + (long long)(n0 + 4 * u) * P);
+            else {
+#pragma unroll
+              for (int I = 0; I < NB; ++I) v[u].v[I] = T(0);
+            }
+          }
+          const bool okr = n0 + lane < N;
+          fl = okr ? ldg_stream(fc + n0 + lane) : T(0);
+          pl = (okr && pc) ? ldg_stream(pc + n0 + lane) : fl;
+        }
+        const double fd = (double)fl;
+        sf += fd;
+        sq = fma(fd, fd, sq);
+        const double dd = (double)(T)(pl - fl);
+        sd = fma(dd, dd, sd);
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+          double vd[NB];
+#pragma unroll
+          for (int I = 0; I < NB; ++I) vd[I] = (double)v[u].v[I];
+          int idx = 0;
+#pragma unroll
+          for (int I = 0; I < NB; ++I)
+#pragma unroll
+            for (int Jb = I; Jb < NB; ++Jb, ++idx) dmma_884(Hc[idx][0], Hc[idx][1], vd[I], vd[Jb]);
+          const double fk = __shfl_sync(0xffffffffu, fd, 4 * u + k);   // f of row n0 + 4u + k
+#pragma unroll
+          for (int I = 0; I < NB; ++I) Gc[I] = fma(vd[I], fk, Gc[I]);
+        }
+      }
+      const double wc = (double)w[wlen == 1 ? 0 : c];
+#pragma unroll
+      for (int i = 0; i < NBT; ++i) { Ht[i][0] = fma(wc, Hc[i][0], Ht[i][0]); Ht[i][1] = fma(wc, Hc[i][1], Ht[i][1]); }
+#pragma unroll
+      for (int I = 0; I < NB; ++I) Gt[I] = fma(wc, Gc[I], Gt[I]);
+      sf = warp_sum(sf);
+      if (lane == 0) sfc[c * NW + warp] = sf;
+    }
+    // ---- warp partials -> shared memory; entry (i, j) of block (I, Jb) is H[NB*gi + I][NB*gj + Jb]
+#pragma unroll
+    for (int I = 0; I < NB; ++I) { Gt[I] += shfl_xor(Gt[I], 1); Gt[I] += shfl_xor(Gt[I], 2); }
+    sd = warp_sum(sd);
+    sq = warp_sum(sq);
+    double* r = red + warp * RW;
+    {
+      int idx = 0;
+#pragma unroll
+      for (int I = 0; I < NB; ++I)
+#pragma unroll
+        for (int Jb = I; Jb < NB; ++Jb, ++idx) {
+          r[(NB * gi + I) * PP + NB * (2 * k) + Jb] = Ht[idx][0];
+          r[(NB * gi + I) * PP + NB * (2 * k + 1) + Jb] = Ht[idx][1];
+        }
+    }
+    if (k == 0) {
+#pragma unroll
+      for (int I = 0; I < NB; ++I) r[PP * PP + NB * gi + I] = Gt[I];
+    }
+    if (lane == 0) { r[PP * PP + PP] = sd; r[PP * PP + PP + 1] = sq; }
+    __syncthreads();
+    for (int e = tid; e < P * P; e += TPB) {
+      const int i = e / P, j = e - i * P;
+      const int lo = min(i, j), hi = max(i, j);
+      // block (lo % NB, hi % NB) was computed iff lo % NB <= hi % NB; otherwise its transpose was
+      const int off = ((lo % NB) <= (hi % NB)) ? lo * PP + hi : hi * PP + lo;
+      double sacc = 0.0;
+#pragma unroll
+      for (int ww = 0; ww < NW; ++ww) sacc += red[ww * RW + off];
+      Hout[b * P * P + e] = (T)sacc;
+    }
+    if (tid < P) {
+      double sacc = 0.0;
+#pragma unroll
+      for (int ww = 0; ww < NW; ++ww) sacc += red[ww * RW + PP * PP + tid];
+      gout[b * P + tid] = (T)sacc;
+    }
+    if (tid == TPB - 1) {
+      double s1 = 0.0, s2 = 0.0, tot = 0.0;
+#pragma unroll
+      for (int ww = 0; ww < NW; ++ww) { s1 += red[ww * RW + PP * PP + PP]; s2 += red[ww * RW + PP * PP + PP + 1]; }
+      for (int c = 0; c < C; ++c) {
+        double sacc = 0.0;
+        for (int ww = 0; ww < NW; ++ww) sacc += sfc[c * NW + ww];
+        tot = fma(sacc, sacc, tot);
+      }
+      stats[b * 4 + 0] = tot; stats[b * 4 + 1] = s1; stats[b * 4 + 2] = s2; stats[b * 4 + 3] = 0.0;
+    }
+    __syncthreads();
+  }
+}
+
 // ======================================================================= cost statistic
 // stat[b] = sum_c (sum_n f[b,c,n])^2  (lma:100).  One warp per (b), lanes stride n.
 template <typename T>
@@ -801,6 +973,19 @@ static int launch_normal_eq(const void* J, const void* f, const void* fprev, con
       kern<<<grid, NWD * 32, smemd, st>>>((const T*)J, (const T*)f, (const T*)fprev, (const T*)w, wlen, B, C, N, P, g, H,
                                           (T*)nullptr, stats, ctrl);
     };
+    // vector-load variant: rows of NB-element groups, every group NB*sizeof(T)-byte aligned
+    const int NBv = P <= 16 ? 2 : 4;
+    if (P % NBv == 0 && aligned_to(J, NBv * sizeof(T))) {
+      auto gov = [&](auto kern, int PPv) {
+        const size_t smv = ((size_t)NWD * (PPv * PPv + PPv + 2) + (size_t)C * NWD) * 8;
+        const int grid = occupancy_grid(kern, NWD * 32, smv, B);
+        kern<<<grid, NWD * 32, smv, st>>>((const T*)J, (const T*)f, (const T*)fprev, (const T*)w, wlen, B, C, N, P, (T*)g, (T*)H,
+                                          stats, ctrl);
+      };
+      if (NBv == 2) gov(k_normal_eq_dmma_vec<T, 2, NWD>, 16);
+      else gov(k_normal_eq_dmma_vec<T, 4, NWD>, 32);
+      return check_launch("nlls_normal_eq(dmma_vec)");
+    }
     if (NB == 2) go(k_normal_eq_dmma<T, 2, NWD, 4, false>);
     else if (NB == 3) go(k_normal_eq_dmma<T, 3, NWD, 2, false>);
     else go(k_normal_eq_dmma<T, 4, NWD, 2, false>);
