@@ -61,8 +61,8 @@ __device__ __forceinline__ void warp_sum_many(T (&v)[V]) {
 // Transposed ("recursive halving") warp reduction of VP values held by every lane, VP a power of
 // two <= 32: VP - 1 + log2(32/VP) shuffles instead of 5*VP butterflies.  On return v[0] of lane L
 // holds the warp total of value index L >> log2(32/VP); lanes with (L & (32/VP - 1)) == 0 own it.
-template <int VP>
-__device__ __forceinline__ void warp_reduce_transpose(double (&v)[VP]) {
+template <int VP, typename R>
+__device__ __forceinline__ void warp_reduce_transpose(R (&v)[VP]) {
   static_assert(VP >= 1 && VP <= 32 && (VP & (VP - 1)) == 0, "VP must be a power of two <= 32");
   const int lane = threadIdx.x & 31;
   int m = 16;
@@ -71,8 +71,8 @@ __device__ __forceinline__ void warp_reduce_transpose(double (&v)[VP]) {
     const bool upper = (lane & m) != 0;
 #pragma unroll
     for (int i = 0; i < n / 2; ++i) {
-      const double keep = upper ? v[i + n / 2] : v[i];
-      const double send = upper ? v[i] : v[i + n / 2];
+      const R keep = upper ? v[i + n / 2] : v[i];
+      const R send = upper ? v[i] : v[i + n / 2];
       v[i] = keep + shfl_xor(send, m);
     }
   }

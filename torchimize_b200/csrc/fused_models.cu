@@ -10,6 +10,7 @@
 // (newton_parallel.py:40-43 applied to tests/unit_test_parallel.py:53-65,105-118).  HBM traffic per
 // iteration: y once, f_prev once (read), f once (write) — 3*s*C*N bytes per problem.
 #include <cstdlib>
+#include <type_traits>
 #include "models.cuh"
 #include "rowacc.cuh"
 
@@ -366,6 +367,261 @@ k_model_normal_eq_staged(const T* __restrict__ p, const T* __restrict__ x, const
         stats[b * 4 + 3] = 0.0;
       }
     }
+  }
+}
+
+// ------------------------------------------------------------------ fused normal equations, warp per problem
+// For problems with little work each (C*N of a few thousand samples: cfg-3's N = 1000, C = 1) the CTA-per-problem
+// kernel above spends a fifth of its issue slots in CTA barriers and a quarter in the per-problem epilogue (r01d
+// profile: profiles/r01d_fused_weak.txt).  Here every WARP owns whole problems: a private ring of NSTAGE chunks of
+// CH samples (bulk async copies issued by lane 0, one mbarrier per stage, __syncwarp hand-back), 32 samples per
+// step and lane, one transposed warp reduction per problem and direct global writes — no CTA barrier, no
+// cross-warp shared-memory reduction.  fp32 keeps its per-block partial sums and the warp reduction in fp32 (the
+// reference sums everything in fp32); the cross-block sums of the statistics stay fp64.
+// MODE: WPP_NEQ normal equations (newton_parallel.py:40-43 fused with the model), WPP_GDA cost-summed tall system
+// (gda:134-139), WPP_COST trial cost (lma:99-100).  prevA/prevB are the ping-pong buffers of f [B,C,N] (NEQ) or of the
+// cost-summed f_s [B,N] (GDA); outg/outH are T (NEQ) or fp64 (GDA).
+enum { WPP_NEQ = 0, WPP_GDA = 1, WPP_COST = 2 };
+
+template <typename T, typename Model, int MODE, int SB, int NSTAGE, int NW, bool C1>
+__global__ void __launch_bounds__(NW * 32)
+k_model_wpp(const T* __restrict__ p, const T* __restrict__ x, const T* __restrict__ y, long long ybs, long long ycs,
+            const T* __restrict__ w, int wlen, long long B, int C_, int N, T* prevA, T* prevB, void* __restrict__ outg,
+            void* __restrict__ outH, double* __restrict__ stats, const nlls_ctrl* ctrl, int CH) {
+  if (is_done(ctrl)) return;
+  using TA = typename std::conditional<MODE == WPP_GDA, double, T>::type;      // accumulator type of g / H
+  constexpr int P = Model::P, NH = Tri<P>::N, V = P + NH;
+  constexpr int VP = Pow2Ceil<V>::value, OWN = 32 / VP;
+  static_assert(V <= 32, "model with too many parameters for the transposed reduction");
+  const int C = C1 ? 1 : C_;                 // C1: single cost — no cost loop, per-cost sums in a register
+  const int it = iter_index(ctrl);
+  T* __restrict__ f_out = (MODE == WPP_COST) ? nullptr : ((it & 1) ? prevB : prevA);
+  const T* __restrict__ f_prev = (MODE != WPP_COST && it > 0 && prevA) ? ((it & 1) ? prevA : prevB) : nullptr;
+  const bool has_prev = f_prev != nullptr;
+  const int Cy = (C1 || ycs == 0) ? 1 : C;
+  const int CP = (MODE == WPP_NEQ) ? C : (MODE == WPP_GDA ? 1 : 0);            // rows of "previous" data per chunk
+  const int stage_elems = (Cy + CP) * CH;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  const size_t ring_bytes = (size_t)NSTAGE * stage_elems * sizeof(T);          // CH % 64 == 0: 16-byte granular
+  const bool use_sfc = !C1 && MODE != WPP_GDA;
+  const size_t per_warp = ring_bytes + 64 + (use_sfc ? (size_t)C * 32 * 8 : 0);
+  unsigned char* mine = smem_raw + (size_t)warp * per_warp;
+  T* ring = reinterpret_cast<T*>(mine);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(mine + ring_bytes);
+  double* sfc = reinterpret_cast<double*>(mine + ring_bytes + 64);             // [C][32] per-cost sums of f
+  if (lane == 0) {
+#pragma unroll
+    for (int s = 0; s < NSTAGE; ++s) mbar_init(&bars[s], 1);
+    mbar_fence_init();
+  }
+  __syncwarp();
+  const long long wid = (long long)blockIdx.x * NW + warp, nwarps = (long long)gridDim.x * NW;
+  const int QN = (N + CH - 1) / CH;
+  const long long prev_bs = (MODE == WPP_NEQ) ? (long long)C * N : (long long)N;   // problem stride of prev / f_out
+
+  long long fb = wid;                       // producer cursor: next chunk to request
+  int fq = 0;
+  unsigned fst = 0;
+  auto issue = [&]() {
+    if (fb >= B) return;
+    if (lane == 0) {
+      const int n0 = fq * CH;
+      const unsigned bytes = (unsigned)min(CH, N - n0) * (unsigned)sizeof(T);
+      T* dst = ring + (size_t)fst * stage_elems;
+      mbar_expect_tx(&bars[fst], bytes * (unsigned)(Cy + (has_prev ? CP : 0)));
+      const T* src = y + fb * ybs + n0;
+      for (int c = 0; c < Cy; ++c, src += ycs, dst += CH) bulk_g2s(dst, src, bytes, &bars[fst]);
+      if (has_prev) {
+        const T* ps = f_prev + fb * prev_bs + n0;
+        for (int c = 0; c < CP; ++c, ps += N, dst += CH) bulk_g2s(dst, ps, bytes, &bars[fst]);
+      }
+    }
+    fst = (fst + 1 == NSTAGE) ? 0 : fst + 1;
+    if (++fq == QN) { fq = 0; fb += nwarps; }
+  };
+#pragma unroll
+  for (int s = 0; s < NSTAGE; ++s) issue();
+
+  unsigned st = 0, ph = 0;
+  const T w0 = (MODE == WPP_COST) ? T(1) : w[0];
+  for (long long b = wid; b < B; b += nwarps) {
+    Model M;
+    M.load(p + b * P);
+    RowAcc<TA, P> acc;
+    acc.clear();
+    double sd = 0.0, sq = 0.0, sf1 = 0.0;
+    if (use_sfc)
+      for (int c = 0; c < C; ++c) sfc[c * 32 + lane] = 0.0;
+    T* fo_b = f_out ? f_out + b * prev_bs : nullptr;
+    for (int q = 0; q < QN; ++q) {
+      const int n0 = q * CH, rows = min(CH, N - n0);
+      const T* sy = ring + (size_t)st * stage_elems + lane;
+      const T* sp = sy + Cy * CH;
+      const T* xq = x + n0 + lane;
+      T* fo_q = fo_b ? fo_b + n0 + lane : nullptr;
+      const int ystep = (Cy == 1) ? 0 : CH;
+      bool waited = false;
+      T sd_t = T(0), sq_t = T(0), sf_t = T(0);                                 // fp32: per-chunk partial sums in T
+      auto block = [&](int j0, auto full_tag) {
+        constexpr bool FULL = decltype(full_tag)::value;
+        T m[SB], k[SB][MODE == WPP_COST ? 1 : P];
+#pragma unroll
+        for (int i = 0; i < SB; ++i) {
+          const T xv = ld_cached(FULL ? xq + j0 + i * 32 : x + min(n0 + j0 + i * 32 + lane, N - 1));
+          if constexpr (MODE == WPP_COST) m[i] = M.value(xv);
+          else M.eval(xv, m[i], k[i]);
+        }
+        if (!waited) { mbar_wait(&bars[st], ph); waited = true; }             // first block's model evaluation overlaps the wait
+        const T* yc = sy + j0;
+        const T* pc = sp + j0;
+        T* fo = fo_q ? fo_q + j0 : nullptr;
+        if constexpr (MODE == WPP_COST) {
+          if constexpr (C1) {
+#pragma unroll
+            for (int i = 0; i < SB; ++i)
+              if (FULL || j0 + i * 32 + lane < rows) { const T r = yc[i * 32] - m[i]; sf_t = fma(r, r, sf_t); }
+          } else {
+            for (int c = 0; c < C; ++c, yc += ystep) {
+              T sfl = T(0);
+#pragma unroll
+              for (int i = 0; i < SB; ++i)
+                if (FULL || j0 + i * 32 + lane < rows) { const T r = yc[i * 32] - m[i]; sfl = fma(r, r, sfl); }
+              sfc[c * 32 + lane] += (double)sfl;
+            }
+          }
+        } else if constexpr (MODE == WPP_GDA) {
+          T s1[SB], fs[SB];
+#pragma unroll
+          for (int i = 0; i < SB; ++i) { s1[i] = T(0); fs[i] = T(0); }
+          for (int c = 0; c < C; ++c, yc += ystep) {
+            const T wc = C1 ? w0 : w[wlen == 1 ? 0 : c];
+#pragma unroll
+            for (int i = 0; i < SB; ++i) {
+              const T r = yc[i * 32] - m[i];                 // rows past the chunk hold stale data; masked below
+              s1[i] = fma(wc, r, s1[i]);
+              fs[i] = fma(wc, r * r, fs[i]);                 // gda:136
+            }
+          }
+#pragma unroll
+          for (int i = 0; i < SB; ++i) {
+            if (FULL || j0 + i * 32 + lane < rows) {
+              double jd[P];
+#pragma unroll
+              for (int qq = 0; qq < P; ++qq) jd[qq] = (double)(T(2) * s1[i] * k[i][qq]);   // gda:137 (cost-summed row, in T)
+              acc.add(jd, (double)fs[i], 1.0);
+              if (fo) fo[i * 32] = fs[i];
+              sq_t = fma(fs[i], fs[i], sq_t);
+              if (has_prev) { const T d = pc[i * 32] - fs[i]; sd_t = fma(d, d, sd_t); }
+            }
+          }
+        } else if constexpr (C1) {
+#pragma unroll
+          for (int i = 0; i < SB; ++i) {
+            if (FULL || j0 + i * 32 + lane < rows) {
+              const T r = yc[i * 32] - m[i];
+              const T fv = r * r;
+              if (fo) stg_stream(fo + i * 32, fv);
+              if (has_prev) {
+                const T d = pc[i * 32] - fv;
+                sd_t = fma(d, d, sd_t);
+              }
+              sq_t = fma(fv, fv, sq_t);
+              sf_t += fv;
+              const T wf = w0 * fv;
+              acc.add_scaled(k[i], T(2) * (wf * r), T(4) * wf);
+            }
+          }
+        } else {
+          T s2[SB], s3[SB];
+#pragma unroll
+          for (int i = 0; i < SB; ++i) { s2[i] = T(0); s3[i] = T(0); }
+          for (int c = 0; c < C; ++c, yc += ystep, pc += CH) {
+            const T wc = w[wlen == 1 ? 0 : c];
+            T sfl = T(0);
+#pragma unroll
+            for (int i = 0; i < SB; ++i) {
+              if (FULL || j0 + i * 32 + lane < rows) {
+                const T r = yc[i * 32] - m[i];
+                const T fv = r * r;
+                if (fo) stg_stream(fo + i * 32, fv);
+                if (has_prev) {
+                  const T d = pc[i * 32] - fv;
+                  sd_t = fma(d, d, sd_t);
+                }
+                sq_t = fma(fv, fv, sq_t);
+                sfl += fv;
+                const T wf = wc * fv;
+                s2[i] += wf;
+                s3[i] = fma(wf, r, s3[i]);
+              }
+            }
+            sfc[c * 32 + lane] += (double)sfl;
+            if (fo) fo += N;
+          }
+#pragma unroll
+          for (int i = 0; i < SB; ++i)
+            if (FULL || j0 + i * 32 + lane < rows) acc.add_scaled(k[i], T(2) * s3[i], T(4) * s2[i]);
+        }
+      };
+      int j0 = 0;
+      for (; j0 + 32 * SB <= rows; j0 += 32 * SB) block(j0, std::true_type{});
+      if (j0 < rows) block(j0, std::false_type{});
+      sd += (double)sd_t;
+      sq += (double)sq_t;
+      if constexpr (C1) sf1 += (double)sf_t;
+      if (++st == NSTAGE) { st = 0; ph ^= 1u; }
+      __syncwarp();                          // every lane is done with this stage before it is refilled
+      issue();
+    }
+    // ---- per-problem sums: one transposed warp reduction, totals written straight to global memory
+    double tot = 0.0;
+    if constexpr (MODE != WPP_GDA) {
+      if constexpr (C1) {
+        const double ssum = warp_sum(sf1);
+        tot = ssum * ssum;
+      } else {
+        for (int c = 0; c < C; ++c) {
+          const double ssum = warp_sum(sfc[c * 32 + lane]);
+          tot = fma(ssum, ssum, tot);
+        }
+      }
+    }
+    if constexpr (MODE == WPP_COST) {
+      if (lane == 0) stats[b] = tot;         // stat_out [B]
+    } else {
+      TA v[VP];
+#pragma unroll
+      for (int i = 0; i < P; ++i) v[i] = acc.g[i];
+#pragma unroll
+      for (int i = 0; i < NH; ++i) v[P + i] = acc.h[i];
+#pragma unroll
+      for (int i = V; i < VP; ++i) v[i] = TA(0);
+      warp_reduce_transpose<VP>(v);
+      sd = warp_sum(sd);
+      sq = warp_sum(sq);
+      TA* g = reinterpret_cast<TA*>(outg);
+      TA* H = reinterpret_cast<TA*>(outH);
+      const int vi = lane / OWN;
+      if ((lane & (OWN - 1)) == 0 && vi < V) {
+        if (vi < P) {
+          g[b * P + vi] = v[0];
+        } else {
+          int kk = vi - P, i = 0;
+          while (kk >= P - i) { kk -= P - i; ++i; }
+          const int j = i + kk;
+          H[b * P * P + i * P + j] = v[0];
+          H[b * P * P + j * P + i] = v[0];
+        }
+      }
+      if (lane == 0) {
+        stats[b * 4 + 0] = tot;
+        stats[b * 4 + 1] = sd;
+        stats[b * 4 + 2] = sq;
+        stats[b * 4 + 3] = 0.0;
+      }
+    }
+    __syncwarp();
   }
 }
 
@@ -748,6 +1004,36 @@ static int launch_staged(const ModelArgs& a) {
 }
 
 
+// warp-per-problem variant: chunk size CH (multiple of 64 samples) chosen so that a stage is ~2-4 KB
+template <typename T, typename Model, int MODE>
+static int launch_wpp(const ModelArgs& a) {
+  constexpr int NW = 4, SB = 2, NSTAGE = 3;
+  const size_t es = sizeof(T);
+  const int Cy = a.ycs == 0 ? 1 : a.C;
+  const int CP = MODE == WPP_NEQ ? a.C : (MODE == WPP_GDA ? 1 : 0);
+  const bool ok16 = aligned_to(a.y, 16) && (a.ybs * es) % 16 == 0 && (a.ycs * es) % 16 == 0 && ((size_t)a.N * es) % 16 == 0 &&
+                    (!a.fA || (aligned_to(a.fA, 16) && aligned_to(a.fB, 16)));
+  if (!ok16) return 1;
+  int CH = 64;
+  while (CH < 512 && CH < a.N && (size_t)(Cy + CP) * (CH * 2) * es <= 4096) CH *= 2;
+  const bool c1 = a.C == 1;
+  const bool use_sfc = !c1 && MODE != WPP_GDA;
+  const size_t per_warp = (size_t)NSTAGE * (Cy + CP) * CH * es + 64 + (use_sfc ? (size_t)a.C * 32 * 8 : 0);
+  const size_t smem = per_warp * NW;
+  if (smem > 200 * 1024) return 1;
+  void* og = MODE == WPP_GDA ? (void*)a.g64 : a.g;
+  void* oH = MODE == WPP_GDA ? (void*)a.H64 : a.H;
+  double* os = MODE == WPP_COST ? a.stat_out : a.stats;
+  auto go = [&](auto kern) {
+    const int grid = grid_for(kern, NW * 32, smem, (a.B + NW - 1) / NW);
+    kern<<<grid, NW * 32, smem, a.st>>>((const T*)a.p, (const T*)a.x, (const T*)a.y, a.ybs, a.ycs, (const T*)a.w, a.wlen, a.B,
+                                        a.C, a.N, (T*)a.fA, (T*)a.fB, og, oH, os, a.ctrl, CH);
+  };
+  if (c1) go(k_model_wpp<T, Model, MODE, SB, NSTAGE, NW, true>);
+  else go(k_model_wpp<T, Model, MODE, SB, NSTAGE, NW, false>);
+  return check_launch("nlls_model(wpp)");
+}
+
 template <typename T>
 static bool rows16(const ModelArgs& a) {
   const size_t es = sizeof(T);
@@ -803,6 +1089,11 @@ static int run_op(Op op, const ModelArgs& a) {
       if (smem > 200 * 1024) { set_error("fused model path: too many costs (C=%d)", a.C); return NLLS_E_SHAPE; }
       if (!g_force_direct) {   // bulk-copy staged variant whenever every data row is 16-byte addressable
         int rc = 1;
+        // single-cost problems of a few thousand samples: warp per problem (cfg-3: 2.5 -> 1.8 ms, profiles/r01e)
+        if (fused_variant() == 4 || (fused_variant() == 0 && a.C == 1 && a.N <= 4096)) {
+          rc = launch_wpp<T, Model, WPP_NEQ>(a);
+          if (rc <= 0) return rc;
+        }
         switch (fused_variant()) {
           case 1: rc = launch_staged<T, Model, 256, 2>(a); break;
           case 2: rc = launch_staged<T, Model, 64, 2>(a); break;
@@ -819,6 +1110,10 @@ static int run_op(Op op, const ModelArgs& a) {
     }
     case OP_NEQ_GDA: {
       if (!g_force_direct) {
+        if (fused_variant() == 4 || (fused_variant() == 0 && a.C == 1 && a.N <= 4096)) {
+          const int rcw = launch_wpp<T, Model, WPP_GDA>(a);
+          if (rcw <= 0) return rcw;
+        }
         const int rc = launch_gda_staged<T, Model, 128, 2>(a);
         if (rc <= 0) return rc;
       }
@@ -832,6 +1127,10 @@ static int run_op(Op op, const ModelArgs& a) {
       const size_t smem = ((size_t)a.C * TPB + (size_t)a.C * NW) * 8;
       if (smem > 200 * 1024) { set_error("fused model path: too many costs (C=%d)", a.C); return NLLS_E_SHAPE; }
       if (!g_force_direct) {
+        if (fused_variant() == 4 || (fused_variant() == 0 && a.C == 1 && a.N <= 4096)) {
+          const int rcw = launch_wpp<T, Model, WPP_COST>(a);
+          if (rcw <= 0) return rcw;
+        }
         const int rc = launch_cost_staged<T, Model, 128, 2>(a);
         if (rc <= 0) return rc;
       }

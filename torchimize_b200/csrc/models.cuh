@@ -15,10 +15,43 @@ namespace nlls {
 
 template <typename T> __device__ __forceinline__ T t_exp(T x);
 template <> __device__ __forceinline__ double t_exp<double>(double x) { return exp(x); }
-template <> __device__ __forceinline__ float t_exp<float>(float x) { return expf(x); }
+// fp32: one FMUL + MUFU.EX2.  The rounding of x*log2(e) makes the RELATIVE error grow like |x| * 1e-7, but every
+// use here is exp(-a) with a >= 0 multiplied into the model value, so the ABSOLUTE error is bounded by
+// max_a(a e^-a) * 1e-7 = 4e-8 of the peak amplitude — below one fp32 ulp of the model at its peak.
+template <> __device__ __forceinline__ float t_exp<float>(float x) {
+  float r;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x * 1.4426950408889634f));
+  return r;
+}
 template <typename T> __device__ __forceinline__ T t_erf(T x);
 template <> __device__ __forceinline__ double t_erf<double>(double x) { return erf(x); }
 template <> __device__ __forceinline__ float t_erf<float>(float x) { return erff(x); }
+
+// K(x) = 1 + erf(x) given E = exp(-x^2).
+//   fp64: CUDA's erf (the 1e-9 parity target needs full accuracy).
+//   fp32: branch-free  erfc(|x|) = E * t * Q(t),  t = 1 / (1 + 0.3 |x|),  Q of degree 8 fitted to the scaled
+//         complementary error function erfcx on [0, 10.5] (max relative error 2.0e-8 in exact arithmetic,
+//         4.3e-7 evaluated in fp32); K = erfc(|x|) for x < 0 (no cancellation: relative accuracy in the
+//         left tail, where the reference's own fp32 `1 + erf(x)` rounds to 0) and 2 - erfc(x) otherwise.
+//         ~16 instructions and no divergent branch instead of erff's two-sided ~40, and E is needed for
+//         the derivative anyway.  Fit: least squares with Lawson reweighting on the relative error.
+template <typename T> __device__ __forceinline__ T one_plus_erf(T x, T E);
+template <> __device__ __forceinline__ double one_plus_erf<double>(double x, double) { return 1.0 + erf(x); }
+template <> __device__ __forceinline__ float one_plus_erf<float>(float x, float E) {
+  const float ax = fabsf(x);
+  const float t = __frcp_rn(fmaf(0.3f, ax, 1.0f));
+  float q = -0.12955187585482458f;
+  q = fmaf(q, t, 0.4857163224001443f);
+  q = fmaf(q, t, -0.5126247969354352f);
+  q = fmaf(q, t, 0.5481587242455374f);
+  q = fmaf(q, t, -0.09498945570912465f);
+  q = fmaf(q, t, 0.215089233597969f);
+  q = fmaf(q, t, 0.14829135184669887f);
+  q = fmaf(q, t, 0.17072300956908976f);
+  q = fmaf(q, t, 0.1691874673196955f);
+  const float c = E * (t * q);                    // erfc(|x|)
+  return x < 0.0f ? c : 2.0f - c;
+}
 
 template <typename T>
 struct EmgModel {
@@ -35,15 +68,18 @@ struct EmgModel {
   __device__ __forceinline__ T value(T t) const {
     const T d = t - mu;
     const T G = t_exp<T>(-(d * d) * inv_s2h);                 // gauss_term, emg.py:20
-    const T A = T(1) + t_erf<T>(xs * d);                      // asymm_term, emg.py:21
+    const T x = xs * d;
+    T E = T(0);
+    if constexpr (sizeof(T) == 4) E = t_exp<T>(-(x * x));
+    const T A = one_plus_erf<T>(x, E);                        // asymm_term, emg.py:21
     return alpha * G * A;
   }
   __device__ __forceinline__ void eval(T t, T& m, T (&k)[P]) const {
     const T d = t - mu;
     const T G = t_exp<T>(-(d * d) * inv_s2h);
     const T x = xs * d;
-    const T A = T(1) + t_erf<T>(x);
     const T E = t_exp<T>(-(x * x));                           // erf_term, emg.py:26
+    const T A = one_plus_erf<T>(x, E);
     const T q = d * inv_s;
     const T GA = G * A;
     m = alpha * GA;
@@ -72,15 +108,18 @@ struct SkewGaussModel {
   __device__ __forceinline__ T value(T t) const {
     const T d = t - mean;
     const T S = t_exp<T>(-(d * d) * inv_s2h);                 // :48
-    const T K = T(1) + t_erf<T>(xs * d);                      // :49
+    const T x = xs * d;
+    T E = T(0);
+    if constexpr (sizeof(T) == 4) E = t_exp<T>(-(x * x));
+    const T K = one_plus_erf<T>(x, E);                        // :49
     return amp * S * K + off;
   }
   __device__ __forceinline__ void eval(T t, T& m, T (&k)[P]) const {
     const T d = t - mean;
     const T S = t_exp<T>(-(d * d) * inv_s2h);
     const T x = xs * d;
-    const T K = T(1) + t_erf<T>(x);
     const T E = t_exp<T>(-(x * x));
+    const T K = one_plus_erf<T>(x, E);
     const T q = d * inv_s;
     const T SK = S * K;
     m = amp * SK + off;
