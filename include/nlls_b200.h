@@ -157,6 +157,33 @@ int nlls_model_normal_eq(int model, int dtype, const void* p, int P, const void*
                          void* f_pp0, void* f_pp1, void* g, void* H, double* stats,
                          const nlls_ctrl* ctrl, void* stream);
 
+/* Speculative Levenberg-Marquardt trial evaluation (fused path): ONE pass at the trial point p + h that yields
+ * both halves of what lma:99-100 and the NEXT iteration's newton_parallel.py:38-43 need:
+ *   stats_t[b] = { sum_c (sum_n f_t)^2  (trial cost of the gain ratio, lma:100),
+ *                  sum (f_cur - f_t)^2, sum f_t^2  (the NEXT iteration's fcon sums, lma:110), 0 }
+ *   g_t, H_t   = normal equations at the trial point (what the next iteration uses if the step is accepted;
+ *                a rejected step keeps the current g, H — p did not move — so nothing is recomputed).
+ * sel [B] (bytes): problem b's CURRENT residuals f_cur live in (sel[b] ? f_buf1 : f_buf0); the trial residuals
+ * f_t are written to the other buffer.  nlls_lm_update_spec flips sel[b] on acceptance.  Same arithmetic, in the
+ * same order, as nlls_model_normal_eq at the accepted point: trajectories are bit-identical to the two-pass
+ * schedule (nlls_model_normal_eq + nlls_model_cost_stat) at 2/3 of its HBM traffic. */
+int nlls_model_lm_trial(int model, int dtype, const void* p_trial, int P, const void* x, const void* y,
+                        long long y_bstride, long long y_cstride, const void* wvec, int wlen,
+                        long long B, int C, int N, void* f_buf0, void* f_buf1, const unsigned char* sel,
+                        void* g_t, void* H_t, double* stats_t, const nlls_ctrl* ctrl, void* stream);
+
+/* K3 for the speculative schedule (lma:100-116, 124-152): as nlls_lm_update, with
+ *   rho numerator  = stats[b][0] - stats_t[b][0];
+ *   stop tests on the CURRENT g and stats (pre-step point, lma:108-110) — evaluated before anything is replaced;
+ *   on acceptance (rho > 0): p += h, g <- g_t, H <- H_t, stats[b] <- stats_t[b], sel[b] ^= 1;
+ *   on rejection: stats[b][1] <- 0 (f did not change: the next fcon sees sum (f_prev - f)^2 == 0). */
+int nlls_lm_update_spec(int dtype, void* p, const void* h, void* g, void* H, const void* g_t, const void* H_t,
+                        void* u, void* v, double* stats, const double* stats_t, unsigned char* sel, int meth,
+                        double rho1, double rho2, double beta, double gama,
+                        double ftol, double ptol, double gtol,
+                        long long B, int P, void* p_hist, void* rho_out /*nullable*/,
+                        nlls_ctrl* ctrl, void* stream);
+
 /* GD flavour of the fused kernel: outputs as nlls_normal_eq_gda; fsum_pp are [B,N] ping-pong. */
 int nlls_model_normal_eq_gda(int model, int dtype, const void* p, int P, const void* x, const void* y,
                              long long y_bstride, long long y_cstride,

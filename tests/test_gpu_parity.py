@@ -7,7 +7,7 @@ in fp64, boundary flips reported in fp32."""
 import pytest
 import torch
 
-from helpers import CASES, PLAIN, DT, RTOL, CHAOTIC, load, compare_plist, compare_chaotic, rel_err
+from helpers import CASES, PLAIN, DT, RTOL, TOL, CHAOTIC, load, compare_plist, compare_chaotic, rel_err
 from oracle import nlls_oracle as O
 from oracle import models as M
 
@@ -434,3 +434,30 @@ def test_large_p_cfg4_shape_against_oracle():
         pl = SOLVERS[name](p_d, fun_d, jac_d, max_iter=30)
         tr = getattr(O, name)(p_c, fun_c, jac_c, max_iter=30)
         compare_plist(pl, torch.stack(tr.p_list), 'f64', f'largeP {name}')
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize('meth', ['lev', 'marq'])
+@pytest.mark.parametrize('dn', ['f64', 'f32'])
+def test_speculative_lm_schedule_is_bit_identical_to_two_pass(dn, meth):
+    """nlls_model_lm_trial + nlls_lm_update_spec (one model pass per iteration) against
+    nlls_model_normal_eq + nlls_model_cost_stat + nlls_lm_update: same arithmetic in the same order,
+    so every snapshot has to be bit-identical (incl. rejected steps and buffer-role flips)."""
+    from torchimize_b200.functions.parallel import _engine
+    gold = load('synthetic')
+    dt = DT[dn]
+    t, y, p0, w = (cu(gold[k], dt) for k in ('t', 'y', 'p0', 'wvec'))
+    p0 = p0 * (1 + .3 * torch.sin(torch.arange(p0.numel(), device=DEV, dtype=dt).reshape(p0.shape)))   # provoke rejections
+    emg = EMGModel()
+    outs = []
+    for spec in (True, False):
+        old, _engine.SPECULATIVE_LM = _engine.SPECULATIVE_LM, spec
+        try:
+            p = p0.clone()
+            outs.append(torch.stack(lsq_lma_parallel(p, emg.cost, emg.jac, args=(t, y), wvec=w, meth=meth, max_iter=40, **TOL)))
+        finally:
+            _engine.SPECULATIVE_LM = old
+    assert outs[0].shape == outs[1].shape
+    same = (outs[0] == outs[1]) | (torch.isnan(outs[0]) & torch.isnan(outs[1]))
+    assert bool(same.all())
+    assert bool((outs[0][1:] == outs[0][:-1]).all(dim=2).any()), 'no rejected step in the trajectory: test is vacuous'

@@ -36,6 +36,9 @@ SIGNATURES = {
     'nlls_model_normal_eq': [_i, _i, _vp, _i, _vp, _vp, _ll, _ll, _vp, _i, _ll, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp],
     'nlls_model_normal_eq_gda': [_i, _i, _vp, _i, _vp, _vp, _ll, _ll, _vp, _i, _ll, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp],
     'nlls_model_cost_stat': [_i, _i, _vp, _i, _vp, _vp, _ll, _ll, _ll, _i, _i, _vp, _vp, _vp],
+    'nlls_model_lm_trial': [_i, _i, _vp, _i, _vp, _vp, _ll, _ll, _vp, _i, _ll, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp],
+    'nlls_lm_update_spec': [_i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _d, _d, _d, _d, _d, _d, _d, _ll, _i,
+                            _vp, _vp, _vp, _vp],
 }
 
 _lock = threading.Lock()

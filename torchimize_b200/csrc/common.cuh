@@ -81,6 +81,11 @@ __device__ __forceinline__ void warp_reduce_transpose(R (&v)[VP]) {
 }
 template <int V> struct Pow2Ceil { static constexpr int value = V <= 1 ? 1 : V <= 2 ? 2 : V <= 4 ? 4 : V <= 8 ? 8 : V <= 16 ? 16 : 32; };
 
+// product rounded on its own (never contracted into an FMA): the reference materialises f = r*r before summing it,
+// and every kernel that evaluates the same residual has to produce the same bits whatever the compiler fuses
+__device__ __forceinline__ double mul_rn(double a, double b) { return __dmul_rn(a, b); }
+__device__ __forceinline__ float mul_rn(float a, float b) { return __fmul_rn(a, b); }
+
 // streaming (read-once) global loads: bypass L1 allocation
 __device__ __forceinline__ double ldg_stream(const double* p) {
   double r;

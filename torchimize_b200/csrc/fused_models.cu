@@ -27,12 +27,15 @@ template <typename T, typename Model, int TPB, int S>
 __global__ void __launch_bounds__(TPB)
 k_model_normal_eq(const T* __restrict__ p, const T* __restrict__ x, const T* __restrict__ y, long long ybs,
                   long long ycs, const T* __restrict__ w, int wlen, long long B, int C, int N, T* fA, T* fB,
-                  T* __restrict__ g, T* __restrict__ H, double* __restrict__ stats, const nlls_ctrl* ctrl) {
+                  T* __restrict__ g, T* __restrict__ H, double* __restrict__ stats, const nlls_ctrl* ctrl,
+                  const unsigned char* __restrict__ sel) {
   if (is_done(ctrl)) return;
   constexpr int P = Model::P, NW = TPB / 32, NH = Tri<P>::N, V = P + NH + 2;
   const int it = iter_index(ctrl);
-  T* __restrict__ f_out = (it & 1) ? fB : fA;
-  const T* __restrict__ f_prev = (it > 0 && fA) ? ((it & 1) ? fA : fB) : nullptr;
+  // sel == NULL: buffers alternate with the iteration parity.  sel != NULL (speculative LM trial evaluation):
+  // problem b's current residuals live in (sel[b] ? fB : fA) and the trial residuals go to the other buffer.
+  T* f_out = (it & 1) ? fB : fA;
+  const T* f_prev = (it > 0 && fA) ? ((it & 1) ? fA : fB) : nullptr;
   extern __shared__ double smem[];
   double* red = smem;                  // [NW][V]
   double* sfc = smem + NW * V;         // [C][TPB] per-thread per-cost sums of f
@@ -40,6 +43,7 @@ k_model_normal_eq(const T* __restrict__ p, const T* __restrict__ x, const T* __r
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
 
   for (long long b = blockIdx.x; b < B; b += gridDim.x) {
+    if (sel) { const bool sb = sel[b] != 0; f_prev = sb ? fB : fA; f_out = sb ? fA : fB; }
     Model M;
     M.load(p + b * P);
     RowAcc<T, P> acc;
@@ -67,7 +71,7 @@ k_model_normal_eq(const T* __restrict__ p, const T* __restrict__ x, const T* __r
           const int n = n0 + i * TPB + tid;
           if (n < N) {
             const T r = ld_cached(yc + n) - m[i];
-            const T fv = r * r;
+            const T fv = mul_rn(r, r);
             if (f_out) stg_stream(f_out + seg + n, fv);
             if (f_prev) {
               const T d = ldg_stream(f_prev + seg + n) - fv;
@@ -211,15 +215,16 @@ template <typename T, typename Model, int TPB, int S, int NSTAGE>
 __global__ void __launch_bounds__(TPB)
 k_model_normal_eq_staged(const T* __restrict__ p, const T* __restrict__ x, const T* __restrict__ y, long long ybs,
                          long long ycs, const T* __restrict__ w, int wlen, long long B, int C, int N, T* fA, T* fB,
-                         T* __restrict__ g, T* __restrict__ H, double* __restrict__ stats, const nlls_ctrl* ctrl) {
+                         T* __restrict__ g, T* __restrict__ H, double* __restrict__ stats, const nlls_ctrl* ctrl,
+                         const unsigned char* __restrict__ sel) {
   if (is_done(ctrl)) return;
   constexpr int P = Model::P, NW = TPB / 32, NH = Tri<P>::N, V = P + NH + 2, TN = TPB * S;
   constexpr int VP = Pow2Ceil<V>::value, OWN = 32 / VP;      // transposed reduction: lane L owns value L / OWN
   static_assert(V <= 32, "model with too many parameters for the transposed reduction");
   const int it = iter_index(ctrl);
-  T* __restrict__ f_out = (it & 1) ? fB : fA;
-  const T* __restrict__ f_prev = (it > 0 && fA) ? ((it & 1) ? fA : fB) : nullptr;
-  const bool has_prev = f_prev != nullptr;
+  T* f_out = (it & 1) ? fB : fA;
+  const T* f_prev = (it > 0 && fA) ? ((it & 1) ? fA : fB) : nullptr;
+  const bool has_prev = f_prev != nullptr || sel != nullptr;  // sel: per-problem buffer roles (see k_model_normal_eq)
   const int Cy = (ycs == 0) ? 1 : C;                         // one shared data row, or one per cost
   const int stage_elems = (Cy + C) * TN;                     // [Cy][TN] data rows then [C][TN] f_prev rows
   extern __shared__ __align__(128) unsigned char smem_raw[];
@@ -251,7 +256,7 @@ k_model_normal_eq_staged(const T* __restrict__ p, const T* __restrict__ x, const
     const T* src = y + pb * ybs + pn0;
     for (int c = 0; c < Cy; ++c, src += ycs, dst += TN) bulk_g2s(dst, src, bytes, bar);
     if (has_prev) {
-      const T* ps = f_prev + pb * (long long)C * N + pn0;
+      const T* ps = (sel ? (sel[pb] ? fB : fA) : f_prev) + pb * (long long)C * N + pn0;
       for (int c = 0; c < C; ++c, ps += N, dst += TN) bulk_g2s(dst, ps, bytes, bar);
     }
     pn0 += TN;
@@ -274,6 +279,7 @@ k_model_normal_eq_staged(const T* __restrict__ p, const T* __restrict__ x, const
     double sd = 0.0, sq = 0.0;
     double* my_sfc = sfc + (size_t)pbuf * C * TPB + tid;
     for (int c = 0; c < C; ++c) my_sfc[c * TPB] = 0.0;
+    if (sel) f_out = sel[b] ? fA : fB;
     T* fo_b = f_out ? f_out + b * (long long)C * N : nullptr;
     for (int n0 = 0; n0 < N; n0 += TN) {
       T m[S], k[S][P], s2[S], s3[S];
@@ -297,7 +303,7 @@ k_model_normal_eq_staged(const T* __restrict__ p, const T* __restrict__ x, const
         for (int i = 0; i < S; ++i) {
           if (n0 + i * TPB + tid < N) {
             const T r = yc[i * TPB] - m[i];
-            const T fv = r * r;
+            const T fv = mul_rn(r, r);
             if (fo) stg_stream(fo + i * TPB, fv);
             if (has_prev) {
               const T d = pc[i * TPB] - fv;
@@ -387,7 +393,8 @@ template <typename T, typename Model, int MODE, int SB, int NSTAGE, int NW, bool
 __global__ void __launch_bounds__(NW * 32)
 k_model_wpp(const T* __restrict__ p, const T* __restrict__ x, const T* __restrict__ y, long long ybs, long long ycs,
             const T* __restrict__ w, int wlen, long long B, int C_, int N, T* prevA, T* prevB, void* __restrict__ outg,
-            void* __restrict__ outH, double* __restrict__ stats, const nlls_ctrl* ctrl, int CH) {
+            void* __restrict__ outH, double* __restrict__ stats, const nlls_ctrl* ctrl, int CH,
+            const unsigned char* __restrict__ sel) {
   if (is_done(ctrl)) return;
   using TA = typename std::conditional<MODE == WPP_GDA, double, T>::type;      // accumulator type of g / H
   constexpr int P = Model::P, NH = Tri<P>::N, V = P + NH;
@@ -395,9 +402,9 @@ k_model_wpp(const T* __restrict__ p, const T* __restrict__ x, const T* __restric
   static_assert(V <= 32, "model with too many parameters for the transposed reduction");
   const int C = C1 ? 1 : C_;                 // C1: single cost — no cost loop, per-cost sums in a register
   const int it = iter_index(ctrl);
-  T* __restrict__ f_out = (MODE == WPP_COST) ? nullptr : ((it & 1) ? prevB : prevA);
-  const T* __restrict__ f_prev = (MODE != WPP_COST && it > 0 && prevA) ? ((it & 1) ? prevA : prevB) : nullptr;
-  const bool has_prev = f_prev != nullptr;
+  T* f_out = (MODE == WPP_COST) ? nullptr : ((it & 1) ? prevB : prevA);
+  const T* f_prev = (MODE != WPP_COST && it > 0 && prevA) ? ((it & 1) ? prevA : prevB) : nullptr;
+  const bool has_prev = f_prev != nullptr || sel != nullptr;  // sel (NEQ only): per-problem buffer roles
   const int Cy = (C1 || ycs == 0) ? 1 : C;
   const int CP = (MODE == WPP_NEQ) ? C : (MODE == WPP_GDA ? 1 : 0);            // rows of "previous" data per chunk
   const int stage_elems = (Cy + CP) * CH;
@@ -433,7 +440,7 @@ k_model_wpp(const T* __restrict__ p, const T* __restrict__ x, const T* __restric
       const T* src = y + fb * ybs + n0;
       for (int c = 0; c < Cy; ++c, src += ycs, dst += CH) bulk_g2s(dst, src, bytes, &bars[fst]);
       if (has_prev) {
-        const T* ps = f_prev + fb * prev_bs + n0;
+        const T* ps = (sel ? (sel[fb] ? prevB : prevA) : f_prev) + fb * prev_bs + n0;
         for (int c = 0; c < CP; ++c, ps += N, dst += CH) bulk_g2s(dst, ps, bytes, &bars[fst]);
       }
     }
@@ -453,6 +460,7 @@ k_model_wpp(const T* __restrict__ p, const T* __restrict__ x, const T* __restric
     double sd = 0.0, sq = 0.0, sf1 = 0.0;
     if (use_sfc)
       for (int c = 0; c < C; ++c) sfc[c * 32 + lane] = 0.0;
+    if (sel) f_out = sel[b] ? prevA : prevB;
     T* fo_b = f_out ? f_out + b * prev_bs : nullptr;
     for (int q = 0; q < QN; ++q) {
       const int n0 = q * CH, rows = min(CH, N - n0);
@@ -480,13 +488,13 @@ k_model_wpp(const T* __restrict__ p, const T* __restrict__ x, const T* __restric
           if constexpr (C1) {
 #pragma unroll
             for (int i = 0; i < SB; ++i)
-              if (FULL || j0 + i * 32 + lane < rows) { const T r = yc[i * 32] - m[i]; sf_t = fma(r, r, sf_t); }
+              if (FULL || j0 + i * 32 + lane < rows) { const T r = yc[i * 32] - m[i]; const T fv = mul_rn(r, r); sf_t += fv; }
           } else {
             for (int c = 0; c < C; ++c, yc += ystep) {
               T sfl = T(0);
 #pragma unroll
               for (int i = 0; i < SB; ++i)
-                if (FULL || j0 + i * 32 + lane < rows) { const T r = yc[i * 32] - m[i]; sfl = fma(r, r, sfl); }
+                if (FULL || j0 + i * 32 + lane < rows) { const T r = yc[i * 32] - m[i]; const T fv = mul_rn(r, r); sfl += fv; }
               sfc[c * 32 + lane] += (double)sfl;
             }
           }
@@ -520,7 +528,7 @@ k_model_wpp(const T* __restrict__ p, const T* __restrict__ x, const T* __restric
           for (int i = 0; i < SB; ++i) {
             if (FULL || j0 + i * 32 + lane < rows) {
               const T r = yc[i * 32] - m[i];
-              const T fv = r * r;
+              const T fv = mul_rn(r, r);
               if (fo) stg_stream(fo + i * 32, fv);
               if (has_prev) {
                 const T d = pc[i * 32] - fv;
@@ -543,7 +551,7 @@ k_model_wpp(const T* __restrict__ p, const T* __restrict__ x, const T* __restric
             for (int i = 0; i < SB; ++i) {
               if (FULL || j0 + i * 32 + lane < rows) {
                 const T r = yc[i * 32] - m[i];
-                const T fv = r * r;
+                const T fv = mul_rn(r, r);
                 if (fo) stg_stream(fo + i * 32, fv);
                 if (has_prev) {
                   const T d = pc[i * 32] - fv;
@@ -726,7 +734,7 @@ k_model_cost_stat(const T* __restrict__ p, const T* __restrict__ x, const T* __r
 #pragma unroll
         for (int i = 0; i < S; ++i) {
           const int n = n0 + i * TPB + tid;
-          if (n < N) { const T r = ld_cached(yc + n) - m[i]; sfl += (double)(r * r); }
+          if (n < N) { const T r = ld_cached(yc + n) - m[i]; sfl += (double)mul_rn(r, r); }
         }
         sfc[c * TPB + tid] += sfl;
       }
@@ -780,7 +788,7 @@ k_model_cost_stat_staged(const T* __restrict__ p, const T* __restrict__ x, const
         double sfl = 0.0;
 #pragma unroll
         for (int i = 0; i < S; ++i)
-          if (n0 + i * TPB + tid < N) { const T r = yc[i * TPB] - m[i]; sfl += (double)(r * r); }
+          if (n0 + i * TPB + tid < N) { const T r = yc[i * TPB] - m[i]; sfl += (double)mul_rn(r, r); }
         my_sfc[c * TPB] += sfl;
       }
       if (n0 + TN < N) {
@@ -964,6 +972,7 @@ struct ModelArgs {
   void *fA, *fB, *g, *H;
   double *g64, *H64, *stats, *stat_out;
   void *f_out, *J_out;
+  const unsigned char* sel;          // speculative LM: per-problem current-buffer flags (NULL otherwise)
   const nlls_ctrl* ctrl;
   cudaStream_t st;
 };
@@ -996,7 +1005,7 @@ static int launch_staged(const ModelArgs& a) {
   auto launch = [&](auto kern2) {
     const int grid2 = grid_for(kern2, TPB2, smem2, a.B);
     kern2<<<grid2, TPB2, smem2, a.st>>>((const T*)a.p, (const T*)a.x, (const T*)a.y, a.ybs, a.ycs, (const T*)a.w, a.wlen,
-                                        a.B, a.C, a.N, (T*)a.fA, (T*)a.fB, (T*)a.g, (T*)a.H, a.stats, a.ctrl);
+                                        a.B, a.C, a.N, (T*)a.fA, (T*)a.fB, (T*)a.g, (T*)a.H, a.stats, a.ctrl, a.sel);
   };
   if (three) launch(k_model_normal_eq_staged<T, Model, TPB2, S2, 3>);
   else launch(k_model_normal_eq_staged<T, Model, TPB2, S2, 2>);
@@ -1027,7 +1036,7 @@ static int launch_wpp(const ModelArgs& a) {
   auto go = [&](auto kern) {
     const int grid = grid_for(kern, NW * 32, smem, (a.B + NW - 1) / NW);
     kern<<<grid, NW * 32, smem, a.st>>>((const T*)a.p, (const T*)a.x, (const T*)a.y, a.ybs, a.ycs, (const T*)a.w, a.wlen, a.B,
-                                        a.C, a.N, (T*)a.fA, (T*)a.fB, og, oH, os, a.ctrl, CH);
+                                        a.C, a.N, (T*)a.fA, (T*)a.fB, og, oH, os, a.ctrl, CH, MODE == WPP_NEQ ? a.sel : nullptr);
   };
   if (c1) go(k_model_wpp<T, Model, MODE, SB, NSTAGE, NW, true>);
   else go(k_model_wpp<T, Model, MODE, SB, NSTAGE, NW, false>);
@@ -1105,7 +1114,7 @@ static int run_op(Op op, const ModelArgs& a) {
       auto kern = k_model_normal_eq<T, Model, TPB, S>;
       const int grid = grid_for(kern, TPB, smem, a.B);
       kern<<<grid, TPB, smem, a.st>>>((const T*)a.p, (const T*)a.x, (const T*)a.y, a.ybs, a.ycs, (const T*)a.w, a.wlen, a.B,
-                                      a.C, a.N, (T*)a.fA, (T*)a.fB, (T*)a.g, (T*)a.H, a.stats, a.ctrl);
+                                      a.C, a.N, (T*)a.fA, (T*)a.fB, (T*)a.g, (T*)a.H, a.stats, a.ctrl, a.sel);
       return check_launch("nlls_model_normal_eq");
     }
     case OP_NEQ_GDA: {
@@ -1216,4 +1225,15 @@ extern "C" int nlls_model_cost_stat(int model, int dtype, const void* p_trial, i
   a.stat_out = stat_out; a.ctrl = ctrl; a.st = (cudaStream_t)stream;
   if (!stat_out) { set_error("nlls_model_cost_stat: NULL stat_out"); return NLLS_E_NULL; }
   return dispatch(model, dtype, P, OP_COST, a);
+}
+
+extern "C" int nlls_model_lm_trial(int model, int dtype, const void* p_trial, int P, const void* x, const void* y,
+                                   long long y_bstride, long long y_cstride, const void* wvec, int wlen, long long B, int C,
+                                   int N, void* f_buf0, void* f_buf1, const unsigned char* sel, void* g_t, void* H_t,
+                                   double* stats_t, const nlls_ctrl* ctrl, void* stream) {
+  ModelArgs a{};
+  a.p = p_trial; a.x = x; a.y = y; a.w = wvec; a.ybs = y_bstride; a.ycs = y_cstride; a.B = B; a.C = C; a.N = N; a.wlen = wlen;
+  a.fA = f_buf0; a.fB = f_buf1; a.g = g_t; a.H = H_t; a.stats = stats_t; a.sel = sel; a.ctrl = ctrl; a.st = (cudaStream_t)stream;
+  if (!wvec || !g_t || !H_t || !stats_t || !f_buf0 || !f_buf1 || !sel) { set_error("nlls_model_lm_trial: NULL tensor"); return NLLS_E_NULL; }
+  return dispatch(model, dtype, P, OP_NEQ, a);
 }

@@ -72,7 +72,7 @@ struct EmgModel {
     T E = T(0);
     if constexpr (sizeof(T) == 4) E = t_exp<T>(-(x * x));
     const T A = one_plus_erf<T>(x, E);                        // asymm_term, emg.py:21
-    return alpha * G * A;
+    return alpha * (G * A);                                   // same association as eval(): bit-identical m
   }
   __device__ __forceinline__ void eval(T t, T& m, T (&k)[P]) const {
     const T d = t - mu;
@@ -112,7 +112,7 @@ struct SkewGaussModel {
     T E = T(0);
     if constexpr (sizeof(T) == 4) E = t_exp<T>(-(x * x));
     const T K = one_plus_erf<T>(x, E);                        // :49
-    return amp * S * K + off;
+    return amp * (S * K) + off;                               // same association as eval()
   }
   __device__ __forceinline__ void eval(T t, T& m, T (&k)[P]) const {
     const T d = t - mean;

@@ -193,6 +193,78 @@ __global__ void k_lm_update(T* __restrict__ p, const T* __restrict__ h, const T*
   if (ctrl) block_count_add(ctrl, nc_open, accepted, nc_closed);
 }
 
+// ------------------------------------------------------------- LM update, speculative schedule
+// The fused path evaluates normal equations AND cost at the trial point in one pass (nlls_model_lm_trial); this
+// kernel then only chooses, per problem, between the current and the trial set.  Decisions are taken on the
+// CURRENT g / stats (pre-step point, lma:108-110) before anything is replaced.
+template <typename T>
+__global__ void k_lm_update_spec(T* __restrict__ p, const T* __restrict__ h, T* __restrict__ g, T* __restrict__ H,
+                                 const T* __restrict__ g_t, const T* __restrict__ H_t, T* __restrict__ u,
+                                 T* __restrict__ v, double* __restrict__ stats, const double* __restrict__ stats_t,
+                                 unsigned char* __restrict__ sel, int meth, T rho1, T rho2, T beta, T gama, double ftol,
+                                 T ptol, T gtol, long long B, int P, T* __restrict__ p_hist, T* __restrict__ rho_out,
+                                 nlls_ctrl* ctrl) {
+  if (is_done(ctrl)) return;
+  const int it = iter_index(ctrl);
+  const long long b = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  int nc_open = 0, accepted = 0, nc_closed = 0;
+  if (b < B) {
+    const T* hb = h + b * P;
+    T* gb = g + b * P;
+    T* pb = p + b * P;
+    T ub = u[b], vb = v[b];
+    const T num = (T)stats[b * 4 + 0] - (T)stats_t[b * 4 + 0];   // lma:100 (Q3)
+    T den = T(0);
+    for (int i = 0; i < P; ++i) den = fma(hb[i], ub * hb[i] - gb[i], den);
+    T rho = num / den;
+    const T INF = (T)__longlong_as_double(0x7ff0000000000000LL);
+    if (den == T(0)) rho = (num > T(0)) ? INF : -INF;
+    if (rho_out) rho_out[b] = rho;
+    if (meth == NLLS_LM_LEVENBERG) {
+      if (rho > T(0)) {
+        const T t = T(2) * rho - T(1);
+        const T fac = T(1) - t * t * t;
+        const T third = T(1) / T(3);
+        ub *= (fac > third || fac != fac) ? fac : third;
+        vb = T(2);
+      } else if (rho < T(0)) {
+        ub *= vb;
+        vb *= T(2);
+      }
+    } else {
+      if (rho < rho1) ub *= beta;
+      if (rho > rho2) ub /= gama;
+    }
+    u[b] = ub;
+    v[b] = vb;
+    accepted = rho > T(0);
+    if (accepted)
+      for (int i = 0; i < P; ++i) pb[i] += hb[i];
+    bool gcon, pcon;
+    gp_tests<T>(P, gb, 1, hb, pb, gtol, ptol, gcon, pcon);
+    const bool fcon = (it > 0) && (stats[b * 4 + 1] < ftol * ftol * stats[b * 4 + 2]);
+    nc_open = !(gcon || pcon || fcon);
+    nc_closed = !(gcon || pcon);
+    if (p_hist) {
+      T* snap = p_hist + ((long long)it * B + b) * P;
+      for (int i = 0; i < P; ++i) snap[i] = pb[i];
+    }
+    if (accepted) {                                  // the trial point becomes the current point
+      for (int i = 0; i < P; ++i) gb[i] = g_t[b * P + i];
+      T* Hb = H + b * P * P;
+      const T* Ht = H_t + b * P * P;
+      for (int i = 0; i < P * P; ++i) Hb[i] = Ht[i];
+      stats[b * 4 + 0] = stats_t[b * 4 + 0];
+      stats[b * 4 + 1] = stats_t[b * 4 + 1];
+      stats[b * 4 + 2] = stats_t[b * 4 + 2];
+      sel[b] ^= 1;
+    } else {
+      stats[b * 4 + 1] = 0.0;                        // f unchanged: sum (f_prev - f)^2 == 0 at the next fcon
+    }
+  }
+  if (ctrl) block_count_add(ctrl, nc_open, accepted, nc_closed);
+}
+
 // ---------------------------------------------------------------------------- GN update
 template <typename T>
 __global__ void k_gn_update(T* __restrict__ p, const T* __restrict__ g, const T* __restrict__ H,
@@ -648,4 +720,28 @@ extern "C" int nlls_iter_end(nlls_ctrl* ctrl, int solver, double ftol, void* str
   if (!ctrl) { set_error("nlls_iter_end: NULL ctrl"); return NLLS_E_NULL; }
   k_iter_end<<<1, 1, 0, (cudaStream_t)stream>>>(ctrl, solver, ftol);
   return check_launch("nlls_iter_end");
+}
+
+extern "C" int nlls_lm_update_spec(int dtype, void* p, const void* h, void* g, void* H, const void* g_t, const void* H_t,
+                                   void* u, void* v, double* stats, const double* stats_t, unsigned char* sel, int meth,
+                                   double rho1, double rho2, double beta, double gama, double ftol, double ptol, double gtol,
+                                   long long B, int P, void* p_hist, void* rho_out, nlls_ctrl* ctrl, void* stream) {
+  if (int e = check_bp(dtype, B, P)) return e;
+  if (B == 0) return 0;
+  if (!p || !h || !g || !H || !g_t || !H_t || !u || !v || !stats || !stats_t || !sel) {
+    set_error("nlls_lm_update_spec: NULL tensor"); return NLLS_E_NULL;
+  }
+  const int grid = (int)((B + kUpdTPB - 1) / kUpdTPB);
+  cudaStream_t st = (cudaStream_t)stream;
+  if (dtype == NLLS_F64)
+    k_lm_update_spec<double><<<grid, kUpdTPB, 0, st>>>((double*)p, (const double*)h, (double*)g, (double*)H, (const double*)g_t,
+                                                       (const double*)H_t, (double*)u, (double*)v, stats, stats_t, sel, meth,
+                                                       rho1, rho2, beta, gama, ftol, ptol, gtol, B, P, (double*)p_hist,
+                                                       (double*)rho_out, ctrl);
+  else
+    k_lm_update_spec<float><<<grid, kUpdTPB, 0, st>>>((float*)p, (const float*)h, (float*)g, (float*)H, (const float*)g_t,
+                                                      (const float*)H_t, (float*)u, (float*)v, stats, stats_t, sel, meth,
+                                                      (float)rho1, (float)rho2, (float)beta, (float)gama, ftol, (float)ptol,
+                                                      (float)gtol, B, P, (float*)p_hist, (float*)rho_out, ctrl);
+  return check_launch("nlls_lm_update_spec");
 }

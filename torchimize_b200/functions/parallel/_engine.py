@@ -24,6 +24,7 @@ from ..jacobian import batch_jacobian_approx_t
 GN, LM, GD = _lib.SOLVER_GN, _lib.SOLVER_LM, _lib.SOLVER_GD
 _HIST_CHUNK_BYTES = 256 << 20
 _GROUP = 4                      # fused path: iterations enqueued between flag reads
+SPECULATIVE_LM = True           # fused LM: one model pass per iteration (nlls_model_lm_trial); False = two-pass schedule
 
 
 _default_reduce_hook = None
@@ -182,7 +183,33 @@ def solve(solver, p, function, jac_function, args, wvec, ftol, ptol, gtol, max_i
         else:
             fpp = torch.empty(2, B, C, N, dtype=ws.dtype, device=ws.device)
         launched, done = 0, False
-        while launched < max_iter and not done:
+        spec = solver == LM and SPECULATIVE_LM
+        if spec:
+            # Speculative schedule: ONE model pass per iteration at the trial point yields the trial cost (lma:99-100)
+            # AND the next iteration's normal equations; the update kernel picks per problem (nlls_lm_update_spec).
+            g_t, H_t, stats_t = torch.empty_like(ws.g), torch.empty_like(ws.H), torch.empty_like(ws.stats)
+            sel = torch.zeros(B, dtype=torch.uint8, device=ws.device)
+            _lib.call('nlls_model_normal_eq', mid, code, _lib.ptr(work_p), P, _lib.ptr(x), _lib.ptr(y), ybs, ycs,
+                      _lib.ptr(ws.w), ws.w.numel(), B, C, N, _lib.ptr(fpp[0]), _lib.ptr(fpp[1]), _lib.ptr(ws.g),
+                      _lib.ptr(ws.H), _lib.ptr(ws.stats), ctrl, st())             # iteration 0: f(p0) -> fpp[0], sel == 0
+        while spec and launched < max_iter and not done:
+            hp = ws.hist_base_ptr(launched, max_iter)
+            group = min(check_every, max_iter - launched, ws.hist_room(launched))
+            for _ in range(group):
+                lm_solve()
+                _lib.call('nlls_model_lm_trial', mid, code, _lib.ptr(ws.p_trial), P, _lib.ptr(x), _lib.ptr(y), ybs, ycs,
+                          _lib.ptr(ws.w), ws.w.numel(), B, C, N, _lib.ptr(fpp[0]), _lib.ptr(fpp[1]), _lib.ptr(sel),
+                          _lib.ptr(g_t), _lib.ptr(H_t), _lib.ptr(stats_t), ctrl, st())
+                _lib.call('nlls_lm_update_spec', code, _lib.ptr(work_p), _lib.ptr(ws.h), _lib.ptr(ws.g), _lib.ptr(ws.H),
+                          _lib.ptr(g_t), _lib.ptr(H_t), _lib.ptr(ws.u), _lib.ptr(ws.v), _lib.ptr(ws.stats), _lib.ptr(stats_t),
+                          _lib.ptr(sel), meth, float(lm['rho1']), float(lm['rho2']), float(lm['beta']), float(lm['gama']),
+                          ftol, ptol, gtol, B, P, hp, None, ctrl, st())
+                if reduce_hook is not None:
+                    reduce_hook(ws.ctrl[2:6])
+                _lib.call('nlls_iter_end', ctrl, solver, ftol, st())
+            launched += group
+            done, iters, sing = ws.flags()
+        while not spec and launched < max_iter and not done:
             hp = ws.hist_base_ptr(launched, max_iter)
             group = min(check_every, max_iter - launched, ws.hist_room(launched))
             for _ in range(group):
