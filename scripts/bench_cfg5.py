@@ -89,12 +89,17 @@ def main():
                 launches += n_l
                 del p0, t, y, p
                 torch.cuda.empty_cache()
+            if world > 1:
+                gather_results(finals, args.B)                       # untimed warm-up: NCCL sets its communicator up lazily
+                torch.cuda.synchronize()
+                dist.barrier()
             a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             a.record()
             full = gather_results(finals, args.B) if world > 1 else finals
             b.record()
             torch.cuda.synchronize()
-            total_ms += a.elapsed_time(b)
+            solve_ms, gather_ms = total_ms, a.elapsed_time(b)
+            total_ms += gather_ms
             tm = torch.tensor([total_ms], dtype=torch.float64, device=dev)
             if world > 1:
                 dist.all_reduce(tm, op=dist.ReduceOp.MAX)
@@ -105,7 +110,7 @@ def main():
                 passes = it + (1 if sv == 'lm' else 0)               # speculative LM: one model pass per iteration + the first
                 alg = 3 * es * C * N * mine * passes                 # y + f_cur + f_new per pass
                 print(json.dumps({'case': f'cfg5-{sv}-{dn}', 'B_total': args.B, 'n_gpus': world, 'B_per_gpu': mine,
-                                  'chunks_per_gpu': n_chunks, 'iterations': it, 'ms': ms, 'problems_per_s': args.B / (ms * 1e-3),
+                                  'chunks_per_gpu': n_chunks, 'iterations': it, 'ms': ms, 'solve_ms_rank0': solve_ms, 'gather_ms_rank0': gather_ms, 'problems_per_s': args.B / (ms * 1e-3),
                                   'problem_iters_per_s': args.B * it / (ms * 1e-3),
                                   'whole_solve_GBps_per_gpu': alg / (ms * 1e-3) / 1e9, 'frac_of_measured_hbm': alg / (ms * 1e-3) / 1e9 / peak,
                                   'gpu_launches_rank0': launches, 'finite': ok, 'scaling': 'strong'}), flush=True)
