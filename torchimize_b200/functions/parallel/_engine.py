@@ -88,6 +88,7 @@ class Workspace:
             self.u = torch.empty(B, **kw)
             self.v = torch.empty(B, **kw)
             self.dscale = torch.empty(B, 2, **kw)
+        self._pending, self._last = [], (0, 0, 0)
         self.hist = []                 # (first_iteration, tensor[chunk,B,P])
         self.hist_chunk = max(1, _HIST_CHUNK_BYTES // max(1, B * P * p.element_size()))
 
@@ -118,9 +119,38 @@ class Workspace:
         return out
 
     def flags(self):
-        """(done, iters, singular) — one small device->host read."""
+        """(done, iters, singular) — one small device->host read (synchronises)."""
         d, it, sing = self.ctrl_i32[:3].tolist()
         return d, it, sing
+
+    # Fused path: the flags travel to pinned host memory behind each group of iterations and are looked at ONE group
+    # late, so the device always has a full group queued while the host waits (no drain bubble between groups).  The
+    # price is at most one extra group of launches whose kernels return at once (ctrl->done).
+    def post_flags(self):
+        ring = _pinned_ring(self.device)
+        slot = self._slot = (getattr(self, '_slot', -1) + 1) % ring.shape[0]
+        ring[slot].copy_(self.ctrl_i32[:3], non_blocking=True)
+        ev = torch.cuda.Event()
+        ev.record()
+        self._pending.append((slot, ev))
+
+    def poll_flags(self, lag):
+        ring = _pinned_ring(self.device)
+        while len(self._pending) > lag:
+            slot, ev = self._pending.pop(0)
+            ev.synchronize()
+            self._last = tuple(ring[slot].tolist())
+        return self._last
+
+
+_PINNED = {}
+
+
+def _pinned_ring(device):
+    key = device.index if device.index is not None else torch.cuda.current_device()
+    if key not in _PINNED:
+        _PINNED[key] = torch.zeros(16, 3, dtype=torch.int32).pin_memory()
+    return _PINNED[key]
 
 
 def _check_p(p):
@@ -208,7 +238,8 @@ def solve(solver, p, function, jac_function, args, wvec, ftol, ptol, gtol, max_i
                     reduce_hook(ws.ctrl[2:6])
                 _lib.call('nlls_iter_end', ctrl, solver, ftol, st())
             launched += group
-            done, iters, sing = ws.flags()
+            ws.post_flags()
+            done, iters, sing = ws.poll_flags(lag=1)
         while not spec and launched < max_iter and not done:
             hp = ws.hist_base_ptr(launched, max_iter)
             group = min(check_every, max_iter - launched, ws.hist_room(launched))
@@ -227,8 +258,9 @@ def solve(solver, p, function, jac_function, args, wvec, ftol, ptol, gtol, max_i
                               B, C, N, _lib.ptr(ws.stat_h), ctrl, st())
                 update(hp)
             launched += group
-            done, iters, sing = ws.flags()
-        done, iters, sing = ws.flags()
+            ws.post_flags()
+            done, iters, sing = ws.poll_flags(lag=1)
+        done, iters, sing = ws.poll_flags(lag=0) if ws._pending else ws.flags()
     else:
         # ----------------------------------------------------------------- tensor path
         fun, jac = bind_callables(function, jac_function, args)
