@@ -19,8 +19,28 @@ def jacobian_approx_t(p, f, create_graph=False):
     return _autograd_jacobian(f, p, create_graph)
 
 
+def _forward_batch_jacobian(p, f):
+    """P forward-mode passes (JVPs) instead of the reference's C*N vectorised backward passes: problems are
+    independent, so the tangent e_i applied to EVERY row of p at once yields column i of every per-problem
+    Jacobian.  Same derivative (exact AD, not finite differences); SURVEY.md §8f rank 2."""
+    cols = []
+    for i in range(p.shape[1]):
+        tangent = torch.zeros_like(p)
+        tangent[:, i] = 1
+        cols.append(torch.func.jvp(f, (p,), (tangent,))[1])
+    return torch.stack(cols, dim=-1)
+
+
 def batch_jacobian_approx_t(p, f, create_graph=False):
-    """[B,C,N,P] Jacobian of a batched callable f(p)->[B,C,N]; reference: jacobian.py:36-57."""
+    """[B,C,N,P] Jacobian of a batched callable f(p)->[B,C,N]; reference: jacobian.py:36-57.
+    Forward mode first (P passes); callables forward-mode AD cannot trace fall back to the reference's
+    reverse-mode formulation."""
+    if not create_graph:
+        try:
+            with torch.no_grad():
+                return _forward_batch_jacobian(p.detach(), f)
+        except Exception:                                            # noqa: BLE001  (unsupported op / custom Function)
+            pass
     over_batch = lambda q: f(q).sum(dim=0)
     jac = _autograd_jacobian(over_batch, p, create_graph)       # [C,N,B,P]
     lead = jac.dim() - 2
