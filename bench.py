@@ -10,8 +10,9 @@ N=1024 residuals, P=4 parameters, fp64, tol 1e-8, max_iter 80 (README.rst:80-84)
 (torchimize_b200.functions.lsq_gna_parallel); metric = problems solved per second.
 
   value   whole-job problems/s with inputs resident in HBM (timed with CUDA events, max over ranks)
-  e2e     same call, but every step first copies its inputs (p0, t, y) from pinned host memory and
-          ends with a device->host read of the final parameters
+  e2e     the same solves through torchimize_b200.pipeline.solve_host_batches: every step copies its inputs (p0, t, y)
+          from pinned host memory and reads the final parameters back to the host; the copy of step k+1 overlaps the
+          solve of step k (copy stream, two device slots)
   roofline  dominant kernel of the timed steps, CUDA-event timed per launch INSIDE the timed region
           (sustained clocks); achieved = algorithmic bytes / average launch duration
   cpu_baseline  the oracle (CPU restatement of the reference's torch-op path) on a bounded
@@ -243,22 +244,26 @@ def run_ours(args):
     launches = _lib.launches - launches0
     iters = iters_seen[-1]
 
-    # ---- end-to-end steps: host buffers in, host result out
+    # ---- end-to-end steps: host buffers in, host result out, through the public host-batch call
+    # (torchimize_b200.pipeline.solve_host_batches): every step copies ITS inputs (p0, t, y) from pinned host memory and
+    # reads its finals back; the copy of step k+1 runs on a copy stream while step k solves (two device slots).  The
+    # timed region holds exactly K copies, K solves and K result reads — the first copy is not hidden.
+    from torchimize_b200.pipeline import solve_host_batches
     hp0, ht, hy = (x.cpu().pin_memory() for x in (p0, t, y))
-    h_out = torch.empty(B, P, dtype=dt).pin_memory()
-    d_p, d_t, d_y = torch.empty_like(p0), torch.empty_like(t), torch.empty_like(y)
+    e2e_iters = []
 
-    def step_e2e():
-        d_p.copy_(hp0, non_blocking=True)
-        d_t.copy_(ht, non_blocking=True)
-        d_y.copy_(hy, non_blocking=True)
-        coeffs = solve(d_p, d_t, d_y)
-        h_out.copy_(d_p, non_blocking=True)
-        return coeffs
+    def run_e2e(steps):
+        out = None
+        for out, n_it in solve_host_batches(lsq_gna_parallel, ((hp0, (ht, hy)) for _ in range(steps)), emg.cost, emg.jac,
+                                            wvec=w, ftol=tol, ptol=tol, gtol=tol, max_iter=work['max_iter'], fused=fused):
+            e2e_iters.append(n_it)
+        return out
 
-    e2e_steps = max(1, min(args.steps, 3))
-    step_e2e()
-    ms_e2e, _ = timed(step_e2e, e2e_steps)
+    e2e_steps = max(1, args.steps)
+    run_e2e(2)                                                   # warm-up: slot allocation, pinned result buffers
+    ms_e2e, h_out = timed(lambda: run_e2e(e2e_steps), 1)
+    assert e2e_iters[-1] == iters, f'e2e step ran {e2e_iters[-1]} iterations, resident step {iters}'
+    assert bool(torch.isfinite(h_out).all())
     sampler.stop_flag = True
     sampler.join(timeout=2)
     h2d = (hp0.numel() + ht.numel() + hy.numel()) * esz
@@ -315,7 +320,9 @@ def run_ours(args):
                            'l2': f'inputs {y.numel() * esz / 1e9:.2f} GB per GPU >> 126 MB L2 (no flush needed)',
                            'parallelism': f'B sharded over {world} GPU(s), no per-iteration collective, one all-gather of finals'},
                 'e2e': {'value': e2e_val, 'unit': UNIT, 'h2d_bytes_per_step': h2d, 'd2h_bytes_per_step': d2h,
-                        'ms_per_step': ms_e2e / e2e_steps, 'steps': e2e_steps},
+                        'ms_per_step': ms_e2e / e2e_steps, 'steps': e2e_steps,
+                        'api': 'torchimize_b200.pipeline.solve_host_batches (double-buffered H2D on a copy stream; K copies + '
+                               'K solves + K result reads inside the timed region)'},
                 'gpu_launches': launches, 'roofline': roof, 'clocks': sampler.summary()}
         if world == 1 and not args.no_cpu_baseline:
             line['cpu_baseline'] = cpu_baseline(work)
