@@ -376,6 +376,212 @@ k_model_normal_eq_staged(const T* __restrict__ p, const T* __restrict__ x, const
   }
 }
 
+// ------------------------------------------------------------------ fused normal equations, staged, 128-bit lanes
+// Same tiles, same bulk-copy producer and same per-problem epilogue as k_model_normal_eq_staged, but a thread owns
+// VEC = 16 / sizeof(T) ADJACENT samples of a tile (4 fp32, 2 fp64) instead of S samples TPB apart: one 128-bit LDS per
+// data row and per f_prev row, one 128-bit STG of f and one 128-bit load of the abscissa per thread, tile and cost
+// (the r01d profile of the fp32 kernel counted ~70 thread instructions per (cost, sample), a third of them address
+// arithmetic, per-sample bounds predicates and fp32->fp64 conversions: profiles/r01d_fused_weak.txt, cfg2gnf32).
+// Bulk-copy eligibility already makes N a multiple of VEC, so ONE predicate per thread and tile covers the tail.
+// fp32 keeps the per-tile partial sums of the statistics in fp32 (C*VEC terms; the reference sums them in fp32
+// throughout) and folds them into the fp64 per-problem sums once per tile.
+template <typename T> struct Lane16;
+template <> struct Lane16<float> {
+  static constexpr int VEC = 4;
+  static __device__ __forceinline__ void lds(const float* p, float (&v)[4]) {
+    const float4 q = *reinterpret_cast<const float4*>(p); v[0] = q.x; v[1] = q.y; v[2] = q.z; v[3] = q.w;
+  }
+  static __device__ __forceinline__ void ldg(const float* p, float (&v)[4]) {
+    const float4 q = __ldg(reinterpret_cast<const float4*>(p)); v[0] = q.x; v[1] = q.y; v[2] = q.z; v[3] = q.w;
+  }
+  static __device__ __forceinline__ void stg(float* p, const float (&v)[4]) {
+    asm volatile("st.global.L1::no_allocate.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(p), "f"(v[0]), "f"(v[1]), "f"(v[2]), "f"(v[3]) : "memory");
+  }
+};
+template <> struct Lane16<double> {
+  static constexpr int VEC = 2;
+  static __device__ __forceinline__ void lds(const double* p, double (&v)[2]) {
+    const double2 q = *reinterpret_cast<const double2*>(p); v[0] = q.x; v[1] = q.y;
+  }
+  static __device__ __forceinline__ void ldg(const double* p, double (&v)[2]) {
+    const double2 q = __ldg(reinterpret_cast<const double2*>(p)); v[0] = q.x; v[1] = q.y;
+  }
+  static __device__ __forceinline__ void stg(double* p, const double (&v)[2]) {
+    asm volatile("st.global.L1::no_allocate.v2.f64 [%0], {%1,%2};" ::"l"(p), "d"(v[0]), "d"(v[1]) : "memory");
+  }
+};
+
+template <typename T, typename Model, int TPB, int NSTAGE>
+__global__ void __launch_bounds__(TPB, 512 / TPB)
+k_model_normal_eq_vec(const T* __restrict__ p, const T* __restrict__ x, const T* __restrict__ y, long long ybs,
+                      long long ycs, const T* __restrict__ w, int wlen, long long B, int C, int N, T* fA, T* fB,
+                      T* __restrict__ g, T* __restrict__ H, double* __restrict__ stats, const nlls_ctrl* ctrl,
+                      const unsigned char* __restrict__ sel) {
+  if (is_done(ctrl)) return;
+  constexpr int P = Model::P, NW = TPB / 32, NH = Tri<P>::N, V = P + NH + 2, VEC = Lane16<T>::VEC, TN = TPB * VEC;
+  constexpr int VP = Pow2Ceil<V>::value, OWN = 32 / VP;
+  static_assert(V <= 32, "model with too many parameters for the transposed reduction");
+  const int it = iter_index(ctrl);
+  T* f_out = (it & 1) ? fB : fA;
+  const T* f_prev = (it > 0 && fA) ? ((it & 1) ? fA : fB) : nullptr;
+  const bool has_prev = f_prev != nullptr || sel != nullptr;
+  const int Cy = (ycs == 0) ? 1 : C;
+  const int stage_elems = (Cy + C) * TN;
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  T* ring = reinterpret_cast<T*>(smem_raw);
+  size_t off = (size_t)NSTAGE * stage_elems * sizeof(T);
+  off = (off + 15) & ~(size_t)15;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem_raw + off);
+  double* red = reinterpret_cast<double*>(smem_raw + off + 8 * 8);   // [2][NW][VP]
+  double* sfc = red + 2 * NW * VP;                           // [2][C][TPB] per-thread per-cost sums of f
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+
+  if (tid == 0) {
+#pragma unroll
+    for (int s = 0; s < NSTAGE; ++s) mbar_init(&bars[s], 1);
+    mbar_fence_init();
+  }
+  __syncthreads();
+
+  long long pb = blockIdx.x;
+  int pn0 = 0, pst = 0;
+  auto issue = [&]() {
+    if (pb >= B) return;
+    const int rows = min(TN, N - pn0);
+    const unsigned bytes = (unsigned)rows * (unsigned)sizeof(T);
+    T* dst = ring + (size_t)pst * stage_elems;
+    uint64_t* bar = &bars[pst];
+    mbar_expect_tx(bar, bytes * (unsigned)(Cy + (has_prev ? C : 0)));
+    const T* src = y + pb * ybs + pn0;
+    for (int c = 0; c < Cy; ++c, src += ycs, dst += TN) bulk_g2s(dst, src, bytes, bar);
+    if (has_prev) {
+      const T* ps = (sel ? (sel[pb] ? fB : fA) : f_prev) + pb * (long long)C * N + pn0;
+      for (int c = 0; c < C; ++c, ps += N, dst += TN) bulk_g2s(dst, ps, bytes, bar);
+    }
+    pn0 += TN;
+    if (pn0 >= N) { pn0 = 0; pb += gridDim.x; }
+    pst = (pst + 1 == NSTAGE) ? 0 : pst + 1;
+  };
+  if (tid == 0) {
+#pragma unroll
+    for (int s = 0; s < NSTAGE; ++s) issue();
+  }
+
+  int st = 0, pbuf = 0;
+  unsigned ph = 0;
+  const int ystep = (Cy == 1) ? 0 : TN;
+  for (long long b = blockIdx.x; b < B; b += gridDim.x, pbuf ^= 1) {
+    Model M;
+    M.load(p + b * P);
+    if (tid == 0 && b + gridDim.x < B) prefetch_l1(p + (b + gridDim.x) * P);
+    RowAcc<T, P> acc;
+    acc.clear();
+    double sd = 0.0, sq = 0.0;
+    double* my_sfc = sfc + (size_t)pbuf * C * TPB + tid;
+    for (int c = 0; c < C; ++c) my_sfc[c * TPB] = 0.0;
+    if (sel) f_out = sel[b] ? fA : fB;
+    T* fo_b = f_out ? f_out + b * (long long)C * N : nullptr;
+    for (int n0 = 0; n0 < N; n0 += TN) {
+      const int n = n0 + tid * VEC;
+      const bool live = n < N;                               // N % VEC == 0: the whole lane group is in or out
+      T m[VEC], k[VEC][P], s2[VEC], s3[VEC];
+      if (live) {
+        T xv[VEC];
+        Lane16<T>::ldg(x + n, xv);
+#pragma unroll
+        for (int j = 0; j < VEC; ++j) { M.eval(xv[j], m[j], k[j]); s2[j] = T(0); s3[j] = T(0); }   // overlaps the wait below
+      }
+      mbar_wait(&bars[st], ph);
+      if (live) {
+        const T* yc = ring + (size_t)st * stage_elems + tid * VEC;
+        const T* pc = yc + Cy * TN;
+        T* fo = fo_b ? fo_b + n : nullptr;
+        T sdt = T(0), sqt = T(0);
+        T yv[VEC];
+        Lane16<T>::lds(yc, yv);
+#pragma unroll 2
+        for (int c = 0; c < C; ++c, pc += TN) {
+          const T wc = w[wlen == 1 ? 0 : c];
+          if (c > 0 && ystep) { yc += ystep; Lane16<T>::lds(yc, yv); }
+          T r[VEC], fv[VEC];
+#pragma unroll
+          for (int j = 0; j < VEC; ++j) { r[j] = yv[j] - m[j]; fv[j] = mul_rn(r[j], r[j]); }
+          if (fo) { Lane16<T>::stg(fo, fv); fo += N; }
+          if (has_prev) {
+            T pv[VEC];
+            Lane16<T>::lds(pc, pv);
+#pragma unroll
+            for (int j = 0; j < VEC; ++j) { const T d = pv[j] - fv[j]; sdt = fma(d, d, sdt); }
+          }
+          T sfl = T(0);
+#pragma unroll
+          for (int j = 0; j < VEC; ++j) {
+            sqt = fma(fv[j], fv[j], sqt);
+            sfl += fv[j];
+            const T wf = wc * fv[j];
+            s2[j] += wf;
+            s3[j] = fma(wf, r[j], s3[j]);
+          }
+          my_sfc[c * TPB] += (double)sfl;
+        }
+        sd += (double)sdt;
+        sq += (double)sqt;
+#pragma unroll
+        for (int j = 0; j < VEC; ++j) acc.add_scaled(k[j], T(2) * s3[j], T(4) * s2[j]);
+      }
+      if (n0 + TN < N) {
+        __syncthreads();
+        if (tid == 0) issue();
+      }
+      if (++st == NSTAGE) { st = 0; ph ^= 1u; }
+    }
+    double v[VP];
+#pragma unroll
+    for (int i = 0; i < P; ++i) v[i] = (double)acc.g[i];
+#pragma unroll
+    for (int i = 0; i < NH; ++i) v[P + i] = (double)acc.h[i];
+    v[P + NH] = sd;
+    v[P + NH + 1] = sq;
+#pragma unroll
+    for (int i = V; i < VP; ++i) v[i] = 0.0;
+    warp_reduce_transpose<VP>(v);
+    double* myred = red + (size_t)pbuf * NW * VP;
+    if ((lane & (OWN - 1)) == 0) myred[warp * VP + lane / OWN] = v[0];
+    __syncthreads();
+    if (tid == 0) issue();
+    if (tid < V) {
+      double s = 0.0;
+#pragma unroll
+      for (int kk = 0; kk < NW; ++kk) s += myred[kk * VP + tid];
+      if (tid < P) {
+        g[b * P + tid] = (T)s;
+      } else if (tid < P + NH) {
+        int kk = tid - P, i = 0;
+        while (kk >= P - i) { kk -= P - i; ++i; }
+        const int j = i + kk;
+        H[b * P * P + i * P + j] = (T)s;
+        H[b * P * P + j * P + i] = (T)s;
+      } else {
+        stats[b * 4 + (tid - P - NH) + 1] = s;
+      }
+    } else if (warp == NW - 1) {
+      const double* col = sfc + (size_t)pbuf * C * TPB;
+      double tot = 0.0;
+      for (int c = 0; c < C; ++c) {
+        double s = 0.0;
+#pragma unroll
+        for (int kk = 0; kk < NW; ++kk) s += col[c * TPB + kk * 32 + lane];
+        s = warp_sum(s);
+        tot = fma(s, s, tot);
+      }
+      if (lane == 0) {
+        stats[b * 4 + 0] = tot;
+        stats[b * 4 + 3] = 0.0;
+      }
+    }
+  }
+}
+
 // ------------------------------------------------------------------ fused normal equations, warp per problem
 // For problems with little work each (C*N of a few thousand samples: cfg-3's N = 1000, C = 1) the CTA-per-problem
 // kernel above spends a fifth of its issue slots in CTA barriers and a quarter in the per-problem epilogue (r01d
@@ -814,6 +1020,75 @@ k_model_cost_stat_staged(const T* __restrict__ p, const T* __restrict__ x, const
   }
 }
 
+// ------------------------------------------------------------------ fused trial cost, staged, 128-bit lanes
+// Sibling of k_model_normal_eq_vec: same sample-to-thread map and the same order of every sum that reaches
+// stats[0], so the two-pass and the speculative LM schedules stay bit-identical whichever kernel family runs.
+template <typename T, typename Model, int TPB, int NSTAGE>
+__global__ void __launch_bounds__(TPB)
+k_model_cost_stat_vec(const T* __restrict__ p, const T* __restrict__ x, const T* __restrict__ y, long long ybs,
+                      long long ycs, long long B, int C, int N, double* __restrict__ out, const nlls_ctrl* ctrl) {
+  if (is_done(ctrl)) return;
+  constexpr int P = Model::P, NW = TPB / 32, VEC = Lane16<T>::VEC, TN = TPB * VEC;
+  const int Cy = (ycs == 0) ? 1 : C;
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  using Ring = TileRing<T, TN, NSTAGE>;
+  double* sfc = reinterpret_cast<double*>(smem_raw + Ring::bytes(Cy, 0));    // [2][C][TPB]
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  Ring R;
+  R.init(smem_raw, y, ybs, ycs, Cy, nullptr, 0, 0, 0, B, N);
+  int pbuf = 0;
+  const int ystep = (Cy == 1) ? 0 : TN;
+  for (long long b = blockIdx.x; b < B; b += gridDim.x, pbuf ^= 1) {
+    Model M;
+    M.load(p + b * P);
+    if (tid == 0 && b + gridDim.x < B) prefetch_l1(p + (b + gridDim.x) * P);
+    double* my_sfc = sfc + (size_t)pbuf * C * TPB + tid;
+    for (int c = 0; c < C; ++c) my_sfc[c * TPB] = 0.0;
+    for (int n0 = 0; n0 < N; n0 += TN) {
+      const int n = n0 + tid * VEC;
+      const bool live = n < N;
+      T m[VEC];
+      if (live) {
+        T xv[VEC];
+        Lane16<T>::ldg(x + n, xv);
+#pragma unroll
+        for (int j = 0; j < VEC; ++j) m[j] = M.value(xv[j]);
+      }
+      const T* yc = R.wait() + tid * VEC;
+      if (live) {
+        T yv[VEC];
+        Lane16<T>::lds(yc, yv);
+        for (int c = 0; c < C; ++c) {
+          if (c > 0 && ystep) { yc += ystep; Lane16<T>::lds(yc, yv); }
+          T sfl = T(0);
+#pragma unroll
+          for (int j = 0; j < VEC; ++j) { const T r = yv[j] - m[j]; sfl += mul_rn(r, r); }
+          my_sfc[c * TPB] += (double)sfl;
+        }
+      }
+      if (n0 + TN < N) {
+        __syncthreads();
+        if (tid == 0) R.issue();
+      }
+      R.advance();
+    }
+    __syncthreads();
+    if (tid == 0) R.issue();
+    if (warp == NW - 1) {
+      const double* col = sfc + (size_t)pbuf * C * TPB;
+      double tot = 0.0;
+      for (int c = 0; c < C; ++c) {
+        double s = 0.0;
+#pragma unroll
+        for (int kk = 0; kk < NW; ++kk) s += col[c * TPB + kk * 32 + lane];
+        s = warp_sum(s);
+        tot = fma(s, s, tot);
+      }
+      if (lane == 0) out[b] = tot;
+    }
+  }
+}
+
 // ------------------------------------------------------------------ fused GD flavour, bulk-copy staged
 template <typename T, typename Model, int TPB, int S, int NSTAGE>
 __global__ void __launch_bounds__(TPB)
@@ -986,6 +1261,9 @@ static int fused_variant() {
   return v;
 }
 
+// default kernel family of the CTA-per-problem fused kernels: 128-bit lanes for fp32, strided map for fp64
+template <typename T> static bool vec_family() { return sizeof(T) == 4 && fused_variant() == 0; }
+
 // returns 0 when launched, 1 when the shape is not eligible for bulk copies, or a launch error
 template <typename T, typename Model, int TPB2, int S2>
 static int launch_staged(const ModelArgs& a) {
@@ -1012,6 +1290,31 @@ static int launch_staged(const ModelArgs& a) {
   return check_launch("nlls_model_normal_eq(staged)");
 }
 
+
+// 128-bit-lane staged kernel: same eligibility as launch_staged plus a 16-byte aligned abscissa
+template <typename T, typename Model, int TPB2>
+static int launch_vec(const ModelArgs& a) {
+  constexpr int P = Model::P, V = P + Tri<P>::N + 2, NW2 = TPB2 / 32, TN = TPB2 * Lane16<T>::VEC, VP = Pow2Ceil<V>::value;
+  const size_t es = sizeof(T);
+  const int Cy = a.ycs == 0 ? 1 : a.C;
+  const size_t stage = (size_t)(Cy + a.C) * TN * es;
+  const size_t tail = 16 + 64 + ((size_t)2 * NW2 * VP + (size_t)2 * a.C * TPB2) * 8;
+  const bool ok16 = aligned_to(a.y, 16) && aligned_to(a.x, 16) && (a.ybs * es) % 16 == 0 && (a.ycs * es) % 16 == 0 &&
+                    ((size_t)a.N * es) % 16 == 0 && (!a.fA || (aligned_to(a.fA, 16) && aligned_to(a.fB, 16)));
+  if (!ok16 || NW2 * 32 < V + 32) return 1;
+  const int want_ctas = 512 / TPB2;
+  const bool three = (size_t)want_ctas * (3 * stage + tail + 1024) <= 226 * 1024;
+  const size_t smem2 = (three ? 3 : 2) * stage + tail;
+  if (smem2 > 220 * 1024) return 1;
+  auto launch = [&](auto kern2) {
+    const int grid2 = grid_for(kern2, TPB2, smem2, a.B);
+    kern2<<<grid2, TPB2, smem2, a.st>>>((const T*)a.p, (const T*)a.x, (const T*)a.y, a.ybs, a.ycs, (const T*)a.w, a.wlen,
+                                        a.B, a.C, a.N, (T*)a.fA, (T*)a.fB, (T*)a.g, (T*)a.H, a.stats, a.ctrl, a.sel);
+  };
+  if (three) launch(k_model_normal_eq_vec<T, Model, TPB2, 3>);
+  else launch(k_model_normal_eq_vec<T, Model, TPB2, 2>);
+  return check_launch("nlls_model_normal_eq(vec)");
+}
 
 // warp-per-problem variant: chunk size CH (multiple of 64 samples) chosen so that a stage is ~2-4 KB
 template <typename T, typename Model, int MODE>
@@ -1069,6 +1372,26 @@ static int launch_cost_staged(const ModelArgs& a) {
   return check_launch("nlls_model_cost_stat(staged)");
 }
 
+template <typename T, typename Model, int TPB2>
+static int launch_cost_vec(const ModelArgs& a) {
+  constexpr int TN = TPB2 * Lane16<T>::VEC;
+  if (!rows16<T>(a) || !aligned_to(a.x, 16)) return 1;
+  const int Cy = a.ycs == 0 ? 1 : a.C;
+  const size_t tail = (size_t)2 * a.C * TPB2 * 8;
+  const int want_ctas = 1024 / TPB2;
+  const bool three = (size_t)want_ctas * (TileRing<T, TN, 3>::bytes(Cy, 0) + tail + 1024) <= 226 * 1024;
+  const size_t smem2 = (three ? TileRing<T, TN, 3>::bytes(Cy, 0) : TileRing<T, TN, 2>::bytes(Cy, 0)) + tail;
+  if (smem2 > 220 * 1024) return 1;
+  auto launch = [&](auto kern2) {
+    const int grid2 = grid_for(kern2, TPB2, smem2, a.B);
+    kern2<<<grid2, TPB2, smem2, a.st>>>((const T*)a.p, (const T*)a.x, (const T*)a.y, a.ybs, a.ycs, a.B, a.C, a.N, a.stat_out,
+                                        a.ctrl);
+  };
+  if (three) launch(k_model_cost_stat_vec<T, Model, TPB2, 3>);
+  else launch(k_model_cost_stat_vec<T, Model, TPB2, 2>);
+  return check_launch("nlls_model_cost_stat(vec)");
+}
+
 template <typename T, typename Model, int TPB2, int S2>
 static int launch_gda_staged(const ModelArgs& a) {
   constexpr int P = Model::P, V = P + Tri<P>::N + 2, NW2 = TPB2 / 32, TN = TPB2 * S2, VP = Pow2Ceil<V>::value;
@@ -1107,7 +1430,15 @@ static int run_op(Op op, const ModelArgs& a) {
           case 1: rc = launch_staged<T, Model, 256, 2>(a); break;
           case 2: rc = launch_staged<T, Model, 64, 2>(a); break;
           case 3: rc = launch_staged<T, Model, 64, 4>(a); break;
-          default: rc = launch_staged<T, Model, 128, 2>(a); break;   // 4 CTAs/SM: best of the r01 sweep (profiles/)
+          case 5: rc = launch_vec<T, Model, 128>(a); break;
+          case 6: rc = launch_vec<T, Model, 64>(a); break;
+          case 7: rc = launch_vec<T, Model, 256>(a); break;
+          default:
+            // fp32: 128-bit lanes, 64-thread CTAs (cfg-2 fp32 1.01 -> 0.76 ms, profiles/r01f); fp64 is HBM-bound either
+            // way and measures a little better with the strided map at 4 CTAs/SM (r01 sweeps)
+            if (vec_family<T>()) rc = launch_vec<T, Model, 64>(a);
+            if (rc == 1) rc = launch_staged<T, Model, 128, 2>(a);
+            break;
         }
         if (rc <= 0) return rc;                              // 0 launched, < 0 error, 1 = shape not eligible
       }
@@ -1140,7 +1471,12 @@ static int run_op(Op op, const ModelArgs& a) {
           const int rcw = launch_wpp<T, Model, WPP_COST>(a);
           if (rcw <= 0) return rcw;
         }
-        const int rc = launch_cost_staged<T, Model, 128, 2>(a);
+        int rc = 1;
+        if (vec_family<T>() || fused_variant() == 5 || fused_variant() == 6 || fused_variant() == 7) {
+          rc = fused_variant() == 5 ? launch_cost_vec<T, Model, 128>(a) : fused_variant() == 7 ? launch_cost_vec<T, Model, 256>(a)
+                                                                                              : launch_cost_vec<T, Model, 64>(a);
+        }
+        if (rc == 1) rc = launch_cost_staged<T, Model, 128, 2>(a);
         if (rc <= 0) return rc;
       }
       auto kern = k_model_cost_stat<T, Model, TPB, S>;
