@@ -23,6 +23,24 @@ template <> __device__ __forceinline__ float t_exp<float>(float x) {
   asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x * 1.4426950408889634f));
   return r;
 }
+__device__ __forceinline__ float ex2_approx(float x) {
+  float r;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+  return r;
+}
+// exp(-a c) for a >= 0 with a per-problem constant c prepared once: fp32 folds the sign and log2(e) into the constant
+// (ONE FMUL + MUFU.EX2 per evaluation, no negation instruction); fp64 keeps CUDA's exp on the exactly negated product.
+template <typename T> struct ExpNeg;
+template <> struct ExpNeg<double> {
+  static __device__ __forceinline__ double prep(double c) { return c; }
+  static __device__ __forceinline__ double eval(double a, double c) { return exp(-a * c); }
+  static __device__ __forceinline__ double sq(double x) { return exp(-(x * x)); }
+};
+template <> struct ExpNeg<float> {
+  static __device__ __forceinline__ float prep(float c) { return c * -1.4426950408889634f; }
+  static __device__ __forceinline__ float eval(float a, float cp) { return ex2_approx(a * cp); }
+  static __device__ __forceinline__ float sq(float x) { return ex2_approx((x * x) * -1.4426950408889634f); }
+};
 template <typename T> __device__ __forceinline__ T t_erf(T x);
 template <> __device__ __forceinline__ double t_erf<double>(double x) { return erf(x); }
 template <> __device__ __forceinline__ float t_erf<float>(float x) { return erff(x); }
@@ -39,7 +57,8 @@ template <typename T> __device__ __forceinline__ T one_plus_erf(T x, T E);
 template <> __device__ __forceinline__ double one_plus_erf<double>(double x, double) { return 1.0 + erf(x); }
 template <> __device__ __forceinline__ float one_plus_erf<float>(float x, float E) {
   const float ax = fabsf(x);
-  const float t = __frcp_rn(fmaf(0.3f, ax, 1.0f));
+  float t;                                         // MUFU.RCP alone (1 ulp): __frcp_rn adds a Newton step and a slow-path branch
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(t) : "f"(fmaf(0.3f, ax, 1.0f)));
   float q = -0.12955187585482458f;
   q = fmaf(q, t, 0.4857163224001443f);
   q = fmaf(q, t, -0.5126247969354352f);
@@ -56,29 +75,29 @@ template <> __device__ __forceinline__ float one_plus_erf<float>(float x, float 
 template <typename T>
 struct EmgModel {
   static constexpr int P = 4;
-  T alpha, eta, mu, inv_s, inv_s2h, xs, ce;   // 1/sigma, 1/(2 sigma^2), eta/(sigma sqrt2), sqrt(2/pi)*eta
+  T alpha, eta, mu, inv_s, inv_s2h, xs, ce;   // 1/sigma, ExpNeg-prepared 1/(2 sigma^2), eta/(sigma sqrt2), sqrt(2/pi)*eta
   __device__ __forceinline__ void load(const T* __restrict__ p) {
     alpha = p[0]; mu = p[1]; eta = p[3];
     const T sigma = p[2];
     inv_s = T(1) / sigma;
-    inv_s2h = T(0.5) / (sigma * sigma);
+    inv_s2h = ExpNeg<T>::prep(T(0.5) / (sigma * sigma));
     xs = eta / (sigma * T(1.4142135623730951));
     ce = T(0.7978845608028654) * eta;
   }
   __device__ __forceinline__ T value(T t) const {
     const T d = t - mu;
-    const T G = t_exp<T>(-(d * d) * inv_s2h);                 // gauss_term, emg.py:20
+    const T G = ExpNeg<T>::eval(d * d, inv_s2h);                 // gauss_term, emg.py:20
     const T x = xs * d;
     T E = T(0);
-    if constexpr (sizeof(T) == 4) E = t_exp<T>(-(x * x));
+    if constexpr (sizeof(T) == 4) E = ExpNeg<T>::sq(x);
     const T A = one_plus_erf<T>(x, E);                        // asymm_term, emg.py:21
     return alpha * (G * A);                                   // same association as eval(): bit-identical m
   }
   __device__ __forceinline__ void eval(T t, T& m, T (&k)[P]) const {
     const T d = t - mu;
-    const T G = t_exp<T>(-(d * d) * inv_s2h);
+    const T G = ExpNeg<T>::eval(d * d, inv_s2h);
     const T x = xs * d;
-    const T E = t_exp<T>(-(x * x));                           // erf_term, emg.py:26
+    const T E = ExpNeg<T>::sq(x);                           // erf_term, emg.py:26
     const T A = one_plus_erf<T>(x, E);
     const T q = d * inv_s;
     const T GA = G * A;
@@ -100,25 +119,25 @@ struct SkewGaussModel {
     norm = p[0]; mean = p[1]; skew = p[3];
     const T s = p[2];
     inv_s = T(1) / s;
-    inv_s2h = T(0.5) / (s * s);
+    inv_s2h = ExpNeg<T>::prep(T(0.5) / (s * s));
     xs = skew / (s * T(1.4142135623730951));
     amp = norm / (s * T(2.5066282746310002));                 // skewed_gaussian :47
     off = (NP == 5) ? p[NP - 1] : T(0);
   }
   __device__ __forceinline__ T value(T t) const {
     const T d = t - mean;
-    const T S = t_exp<T>(-(d * d) * inv_s2h);                 // :48
+    const T S = ExpNeg<T>::eval(d * d, inv_s2h);                 // :48
     const T x = xs * d;
     T E = T(0);
-    if constexpr (sizeof(T) == 4) E = t_exp<T>(-(x * x));
+    if constexpr (sizeof(T) == 4) E = ExpNeg<T>::sq(x);
     const T K = one_plus_erf<T>(x, E);                        // :49
     return amp * (S * K) + off;                               // same association as eval()
   }
   __device__ __forceinline__ void eval(T t, T& m, T (&k)[P]) const {
     const T d = t - mean;
-    const T S = t_exp<T>(-(d * d) * inv_s2h);
+    const T S = ExpNeg<T>::eval(d * d, inv_s2h);
     const T x = xs * d;
-    const T E = t_exp<T>(-(x * x));
+    const T E = ExpNeg<T>::sq(x);
     const T K = one_plus_erf<T>(x, E);
     const T q = d * inv_s;
     const T SK = S * K;
