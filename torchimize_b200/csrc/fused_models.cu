@@ -595,7 +595,7 @@ k_model_normal_eq_vec(const T* __restrict__ p, const T* __restrict__ x, const T*
 // cost-summed f_s [B,N] (GDA); outg/outH are T (NEQ) or fp64 (GDA).
 enum { WPP_NEQ = 0, WPP_GDA = 1, WPP_COST = 2 };
 
-template <typename T, typename Model, int MODE, int SB, int NSTAGE, int NW, bool C1>
+template <typename T, typename Model, int MODE, int SB, int NSTAGE, int NW, bool C1, bool VL = false>
 __global__ void __launch_bounds__(NW * 32)
 k_model_wpp(const T* __restrict__ p, const T* __restrict__ x, const T* __restrict__ y, long long ybs, long long ycs,
             const T* __restrict__ w, int wlen, long long B, int C_, int N, T* prevA, T* prevB, void* __restrict__ outg,
@@ -606,6 +606,11 @@ k_model_wpp(const T* __restrict__ p, const T* __restrict__ x, const T* __restric
   constexpr int P = Model::P, NH = Tri<P>::N, V = P + NH;
   constexpr int VP = Pow2Ceil<V>::value, OWN = 32 / VP;
   static_assert(V <= 32, "model with too many parameters for the transposed reduction");
+  // VL ("vector lanes", single-cost problems only): a lane owns SB = 16/sizeof(T) ADJACENT samples of a block of 32*SB, so
+  // the abscissa, the data row and the previous residuals arrive with one 128-bit load each and f leaves with one
+  // 128-bit store per lane and block; otherwise lane L owns samples L, L+32, ... (scalar accesses).
+  static_assert(!VL || (C1 && SB * sizeof(T) == 16), "vector lanes: single cost, SB = 16 / sizeof(T)");
+  constexpr int ISTR = VL ? 1 : 32;          // distance between a lane's consecutive samples
   const int C = C1 ? 1 : C_;                 // C1: single cost — no cost loop, per-cost sums in a register
   const int it = iter_index(ctrl);
   T* f_out = (MODE == WPP_COST) ? nullptr : ((it & 1) ? prevB : prevA);
@@ -615,6 +620,7 @@ k_model_wpp(const T* __restrict__ p, const T* __restrict__ x, const T* __restric
   const int CP = (MODE == WPP_NEQ) ? C : (MODE == WPP_GDA ? 1 : 0);            // rows of "previous" data per chunk
   const int stage_elems = (Cy + CP) * CH;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int l0 = VL ? lane * SB : lane;      // a lane's first sample within a block
   extern __shared__ __align__(128) unsigned char smem_raw[];
   const size_t ring_bytes = (size_t)NSTAGE * stage_elems * sizeof(T);          // CH % 64 == 0: 16-byte granular
   const bool use_sfc = !C1 && MODE != WPP_GDA;
@@ -670,19 +676,29 @@ k_model_wpp(const T* __restrict__ p, const T* __restrict__ x, const T* __restric
     T* fo_b = f_out ? f_out + b * prev_bs : nullptr;
     for (int q = 0; q < QN; ++q) {
       const int n0 = q * CH, rows = min(CH, N - n0);
-      const T* sy = ring + (size_t)st * stage_elems + lane;
+      const T* sy = ring + (size_t)st * stage_elems + l0;
       const T* sp = sy + Cy * CH;
-      const T* xq = x + n0 + lane;
-      T* fo_q = fo_b ? fo_b + n0 + lane : nullptr;
+      const T* xq = x + n0 + l0;
+      T* fo_q = fo_b ? fo_b + n0 + l0 : nullptr;
       const int ystep = (Cy == 1) ? 0 : CH;
       bool waited = false;
       T sd_t = T(0), sq_t = T(0), sf_t = T(0);                                 // fp32: per-chunk partial sums in T
       auto block = [&](int j0, auto full_tag) {
         constexpr bool FULL = decltype(full_tag)::value;
         T m[SB], k[SB][MODE == WPP_COST ? 1 : P];
+        [[maybe_unused]] T xl[SB], yl[SB], pl[SB], fl[SB];   // VL: the lane's 16 bytes of x, y, f_prev, f
+        if constexpr (VL) {
+          if (FULL || j0 + l0 < rows) Lane16<T>::ldg(xq + j0, xl);           // rows % SB == 0: a lane is all in or all out
+          else {
+#pragma unroll
+            for (int i = 0; i < SB; ++i) xl[i] = T(0);
+          }
+        }
 #pragma unroll
         for (int i = 0; i < SB; ++i) {
-          const T xv = ld_cached(FULL ? xq + j0 + i * 32 : x + min(n0 + j0 + i * 32 + lane, N - 1));
+          T xv;
+          if constexpr (VL) xv = xl[i];
+          else xv = ld_cached(FULL ? xq + j0 + i * 32 : x + min(n0 + j0 + i * 32 + lane, N - 1));
           if constexpr (MODE == WPP_COST) m[i] = M.value(xv);
           else M.eval(xv, m[i], k[i]);
         }
@@ -690,11 +706,15 @@ k_model_wpp(const T* __restrict__ p, const T* __restrict__ x, const T* __restric
         const T* yc = sy + j0;
         const T* pc = sp + j0;
         T* fo = fo_q ? fo_q + j0 : nullptr;
+        if constexpr (VL) {
+          Lane16<T>::lds(yc, yl);                                             // stale past `rows`, masked below
+          if (MODE != WPP_COST && has_prev) Lane16<T>::lds(pc, pl);
+        }
         if constexpr (MODE == WPP_COST) {
           if constexpr (C1) {
 #pragma unroll
             for (int i = 0; i < SB; ++i)
-              if (FULL || j0 + i * 32 + lane < rows) { const T r = yc[i * 32] - m[i]; const T fv = mul_rn(r, r); sf_t += fv; }
+              if (FULL || j0 + i * ISTR + l0 < rows) { const T r = (VL ? yl[i] : yc[i * 32]) - m[i]; const T fv = mul_rn(r, r); sf_t += fv; }
           } else {
             for (int c = 0; c < C; ++c, yc += ystep) {
               T sfl = T(0);
@@ -712,32 +732,34 @@ k_model_wpp(const T* __restrict__ p, const T* __restrict__ x, const T* __restric
             const T wc = C1 ? w0 : w[wlen == 1 ? 0 : c];
 #pragma unroll
             for (int i = 0; i < SB; ++i) {
-              const T r = yc[i * 32] - m[i];                 // rows past the chunk hold stale data; masked below
+              const T r = (VL ? yl[i] : yc[i * 32]) - m[i];  // rows past the chunk hold stale data; masked below
               s1[i] = fma(wc, r, s1[i]);
               fs[i] = fma(wc, r * r, fs[i]);                 // gda:136
             }
           }
 #pragma unroll
           for (int i = 0; i < SB; ++i) {
-            if (FULL || j0 + i * 32 + lane < rows) {
+            if (FULL || j0 + i * ISTR + l0 < rows) {
               double jd[P];
 #pragma unroll
               for (int qq = 0; qq < P; ++qq) jd[qq] = (double)(T(2) * s1[i] * k[i][qq]);   // gda:137 (cost-summed row, in T)
               acc.add(jd, (double)fs[i], 1.0);
-              if (fo) fo[i * 32] = fs[i];
+              if constexpr (!VL) { if (fo) fo[i * 32] = fs[i]; }
               sq_t = fma(fs[i], fs[i], sq_t);
-              if (has_prev) { const T d = pc[i * 32] - fs[i]; sd_t = fma(d, d, sd_t); }
+              if (has_prev) { const T d = (VL ? pl[i] : pc[i * 32]) - fs[i]; sd_t = fma(d, d, sd_t); }
             }
           }
+          if constexpr (VL) { if (fo && (FULL || j0 + l0 < rows)) Lane16<T>::stg(fo, fs); }
         } else if constexpr (C1) {
 #pragma unroll
           for (int i = 0; i < SB; ++i) {
-            if (FULL || j0 + i * 32 + lane < rows) {
-              const T r = yc[i * 32] - m[i];
+            if (FULL || j0 + i * ISTR + l0 < rows) {
+              const T r = (VL ? yl[i] : yc[i * 32]) - m[i];
               const T fv = mul_rn(r, r);
-              if (fo) stg_stream(fo + i * 32, fv);
+              if constexpr (VL) fl[i] = fv;
+              else if (fo) stg_stream(fo + i * 32, fv);
               if (has_prev) {
-                const T d = pc[i * 32] - fv;
+                const T d = (VL ? pl[i] : pc[i * 32]) - fv;
                 sd_t = fma(d, d, sd_t);
               }
               sq_t = fma(fv, fv, sq_t);
@@ -746,6 +768,7 @@ k_model_wpp(const T* __restrict__ p, const T* __restrict__ x, const T* __restric
               acc.add_scaled(k[i], T(2) * (wf * r), T(4) * wf);
             }
           }
+          if constexpr (VL) { if (fo && (FULL || j0 + l0 < rows)) Lane16<T>::stg(fo, fl); }
         } else {
           T s2[SB], s3[SB];
 #pragma unroll
@@ -1316,6 +1339,13 @@ static int launch_vec(const ModelArgs& a) {
   return check_launch("nlls_model_normal_eq(vec)");
 }
 
+// tuning hook: NLLS_WPP_VL=0 keeps the scalar lane map of the warp-per-problem kernels
+static bool wpp_vector_lanes() {
+  static int v = -1;
+  if (v < 0) { const char* e = getenv("NLLS_WPP_VL"); v = e ? atoi(e) : 1; }
+  return v != 0;
+}
+
 // warp-per-problem variant: chunk size CH (multiple of 64 samples) chosen so that a stage is ~2-4 KB
 template <typename T, typename Model, int MODE>
 static int launch_wpp(const ModelArgs& a) {
@@ -1326,9 +1356,11 @@ static int launch_wpp(const ModelArgs& a) {
   const bool ok16 = aligned_to(a.y, 16) && (a.ybs * es) % 16 == 0 && (a.ycs * es) % 16 == 0 && ((size_t)a.N * es) % 16 == 0 &&
                     (!a.fA || (aligned_to(a.fA, 16) && aligned_to(a.fB, 16)));
   if (!ok16) return 1;
-  int CH = 64;
-  while (CH < 512 && CH < a.N && (size_t)(Cy + CP) * (CH * 2) * es <= 4096) CH *= 2;
   const bool c1 = a.C == 1;
+  // single-cost problems with a 16-byte aligned abscissa: vector lanes (blocks of 32 * 16/sizeof(T) samples)
+  const bool vl = c1 && aligned_to(a.x, 16) && wpp_vector_lanes();
+  int CH = vl ? 128 : 64;
+  while (CH < 512 && CH < a.N && (size_t)(Cy + CP) * (CH * 2) * es <= 4096) CH *= 2;
   const bool use_sfc = !c1 && MODE != WPP_GDA;
   const size_t per_warp = (size_t)NSTAGE * (Cy + CP) * CH * es + 64 + (use_sfc ? (size_t)a.C * 32 * 8 : 0);
   const size_t smem = per_warp * NW;
@@ -1341,7 +1373,8 @@ static int launch_wpp(const ModelArgs& a) {
     kern<<<grid, NW * 32, smem, a.st>>>((const T*)a.p, (const T*)a.x, (const T*)a.y, a.ybs, a.ycs, (const T*)a.w, a.wlen, a.B,
                                         a.C, a.N, (T*)a.fA, (T*)a.fB, og, oH, os, a.ctrl, CH, MODE == WPP_NEQ ? a.sel : nullptr);
   };
-  if (c1) go(k_model_wpp<T, Model, MODE, SB, NSTAGE, NW, true>);
+  if (vl) go(k_model_wpp<T, Model, MODE, 16 / (int)sizeof(T), NSTAGE, NW, true, true>);
+  else if (c1) go(k_model_wpp<T, Model, MODE, SB, NSTAGE, NW, true>);
   else go(k_model_wpp<T, Model, MODE, SB, NSTAGE, NW, false>);
   return check_launch("nlls_model(wpp)");
 }
