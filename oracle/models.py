@@ -127,3 +127,31 @@ def skewgauss_jac(p, x, y):
     dm = torch.stack(dm, dim=-1)
     r = y - m
     return (-2 * r[..., None] * dm)[:, None, :, :]
+
+
+# ------------------------------------------------------- Gaussian on a constant baseline
+# Not a reference model: the CPU statement of torchimize_b200/user_models/gauss_offset.cuh, the example functor
+# of the compiled-model path, written with the reference's cost convention
+# (squared error used as residual, tests/unit_test_parallel.py:40,105-118).  p = [a, mu, sigma, c].
+def gauss_offset_model(p, x):
+    a, mu, sigma, c = _cols(p)
+    return a * torch.exp(-(x - mu) ** 2 / (2 * sigma ** 2)) + c
+
+
+def gauss_offset_cost(p, x, y, n_costs=None):
+    f = (_as_bcn(y, p) - gauss_offset_model(p, x)[:, None, :]) ** 2
+    if n_costs is not None and f.shape[1] == 1:
+        f = f.expand(-1, n_costs, -1).contiguous()
+    return f
+
+
+def gauss_offset_jac(p, x, y, n_costs=None):
+    a, mu, sigma, c = _cols(p)
+    d = x - mu
+    G = torch.exp(-d ** 2 / (2 * sigma ** 2))
+    dm = torch.stack([G, a * G * d / sigma ** 2, a * G * d ** 2 / sigma ** 3, torch.ones_like(G)], dim=-1)   # [B,N,4]
+    r = _as_bcn(y, p) - (a * G + c)[:, None, :]
+    J = -2 * r[..., None] * dm[:, None, :, :]
+    if n_costs is not None and J.shape[1] == 1:
+        J = J.expand(-1, n_costs, -1, -1).contiguous()
+    return J

@@ -14,7 +14,7 @@ CSRC = os.path.join(_HERE, 'csrc')
 F32, F64 = 0, 1
 SOLVER_GN, SOLVER_LM, SOLVER_GD = 0, 1, 2
 LM_LEVENBERG, LM_MARQUARDT = 0, 1
-MODEL_EMG, MODEL_SKEWGAUSS = 0, 1
+MODEL_EMG, MODEL_SKEWGAUSS, MODEL_USER = 0, 1, 100
 CTRL_BYTES = 48
 
 _vp, _i, _ll, _d = ctypes.c_void_p, ctypes.c_int, ctypes.c_longlong, ctypes.c_double
@@ -84,6 +84,62 @@ def load():
     return _lib
 
 
+JIT_DIR = os.path.join(_HERE, '_jit')
+PLUGIN_ENTRY_POINTS = ('nlls_model_eval', 'nlls_model_normal_eq', 'nlls_model_normal_eq_gda', 'nlls_model_cost_stat',
+                       'nlls_model_lm_trial')
+_plugins = {}
+
+
+def build_plugin(source: str, name: str = 'user', verbose=False):
+    """Compile the fused-model kernels (csrc/fused_models.cu) for ONE user-supplied device functor
+    ``nlls::UserModel<T>`` into an in-tree plugin library exporting the nlls_model_* entry points of
+    include/nlls_b200.h.  Cached by a hash of the functor source and of the kernel sources."""
+    import hashlib
+    h = hashlib.sha1(source.encode())
+    for fn in ('fused_models.cu', 'models.cuh', 'common.cuh', 'rowacc.cuh', 'api.cu'):
+        with open(os.path.join(CSRC, fn), 'rb') as f:
+            h.update(f.read())
+    with open(os.path.join(_HERE, '..', 'include', 'nlls_b200.h'), 'rb') as f:
+        h.update(f.read())
+    safe = ''.join(ch if ch.isalnum() else '_' for ch in name)[:40]
+    out_dir = os.path.join(JIT_DIR, f'{safe}_{h.hexdigest()[:16]}')
+    so = os.path.join(out_dir, 'libnlls_user.so')
+    if os.path.exists(so):
+        return so
+    os.makedirs(out_dir, exist_ok=True)
+    hdr = os.path.join(out_dir, 'user_model.cuh')
+    with open(hdr, 'w') as f:
+        f.write(source)
+    tmp = so + f'.tmp{os.getpid()}'
+    cmd = ['nvcc', '-O3', '-std=c++17', '-gencode', 'arch=compute_100a,code=sm_100a', '-lineinfo', '-Xcompiler', '-fPIC',
+           f'-DNLLS_USER_MODEL_HEADER="{hdr}"', '-I', CSRC, '-shared', '-o', tmp,
+           os.path.join(CSRC, 'fused_models.cu'), os.path.join(CSRC, 'api.cu'), '-lcudart']
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    if r.returncode != 0:
+        raise NllsError(f'compiling user model {name!r} failed:\n' + r.stdout[-3000:] + r.stderr[-6000:])
+    os.replace(tmp, so)
+    if verbose:
+        print('built', so)
+    return so
+
+
+def load_plugin(path):
+    """ctypes handle of a plugin library (RTLD_LOCAL: its nlls_* symbols do not clash with libnlls_b200.so)."""
+    with _lock:
+        if path not in _plugins:
+            lib = ctypes.CDLL(path, mode=ctypes.RTLD_LOCAL)
+            for name in PLUGIN_ENTRY_POINTS:
+                fn = getattr(lib, name)
+                fn.argtypes = SIGNATURES[name]
+                fn.restype = _i
+            lib.nlls_last_error.restype = ctypes.c_char_p
+            lib.nlls_last_error.argtypes = []
+            lib.nlls_user_model_params.restype = _i
+            lib.nlls_set_force_direct.argtypes = [_i]
+            _plugins[path] = lib
+    return _plugins[path]
+
+
 def dtype_code(t: torch.Tensor) -> int:
     if t.dtype == torch.float64:
         return F64
@@ -121,10 +177,11 @@ def timing_records():
     return [(n, a.elapsed_time(b)) for n, a, b in (_timing or [])]
 
 
-def call(name, *args):
-    """Invoke an entry point on the current stream of the current device; raise on error."""
+def call(name, *args, lib=None):
+    """Invoke an entry point on the current stream of the current device; raise on error.
+    lib: a plugin library handle (load_plugin) for the nlls_model_* entry points of a user model."""
     global launches
-    lib = load()
+    lib = lib or load()
     if _timing is not None:
         a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         a.record()

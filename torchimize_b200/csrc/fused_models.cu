@@ -14,6 +14,17 @@
 #include "models.cuh"
 #include "rowacc.cuh"
 
+// Plugin build (torchimize_b200.models.compile_model): the same kernels and the same entry points, instantiated for ONE
+// user-supplied device functor nlls::UserModel<T> instead of the built-in models.  The functor follows models.cuh:
+//   static constexpr int P;  void load(const T* p);  T value(T x) const;  void eval(T x, T& m, T (&k)[P]) const  (k = -dm/dp)
+// and may use every helper of models.cuh (ExpNeg, one_plus_erf, ...).  value() and eval() have to return the same bits for m.
+#ifdef NLLS_USER_MODEL_HEADER
+#include NLLS_USER_MODEL_HEADER
+namespace nlls { int g_force_direct = 0; }
+extern "C" int nlls_user_model_params(void) { return nlls::UserModel<double>::P; }
+extern "C" int nlls_set_force_direct(int on) { const int old = nlls::g_force_direct; nlls::g_force_direct = on; return old; }
+#endif
+
 namespace nlls {
 
 constexpr int kFusedTPB = 128;
@@ -1460,12 +1471,14 @@ static int run_op(Op op, const ModelArgs& a) {
           if (rc <= 0) return rc;
         }
         switch (fused_variant()) {
+#ifndef NLLS_USER_MODEL_HEADER                               // tuning variants: built-in models only (plugin compile time)
           case 1: rc = launch_staged<T, Model, 256, 2>(a); break;
           case 2: rc = launch_staged<T, Model, 64, 2>(a); break;
           case 3: rc = launch_staged<T, Model, 64, 4>(a); break;
           case 5: rc = launch_vec<T, Model, 128>(a); break;
           case 6: rc = launch_vec<T, Model, 64>(a); break;
           case 7: rc = launch_vec<T, Model, 256>(a); break;
+#endif
           default:
             // fp32: 128-bit lanes, 64-thread CTAs (cfg-2 fp32 1.01 -> 0.76 ms, profiles/r01f); fp64 is HBM-bound either
             // way and measures a little better with the strided map at 4 CTAs/SM (r01 sweeps)
@@ -1505,10 +1518,13 @@ static int run_op(Op op, const ModelArgs& a) {
           if (rcw <= 0) return rcw;
         }
         int rc = 1;
-        if (vec_family<T>() || fused_variant() == 5 || fused_variant() == 6 || fused_variant() == 7) {
-          rc = fused_variant() == 5 ? launch_cost_vec<T, Model, 128>(a) : fused_variant() == 7 ? launch_cost_vec<T, Model, 256>(a)
-                                                                                              : launch_cost_vec<T, Model, 64>(a);
-        }
+#ifndef NLLS_USER_MODEL_HEADER
+        if (fused_variant() == 5) rc = launch_cost_vec<T, Model, 128>(a);
+        else if (fused_variant() == 7) rc = launch_cost_vec<T, Model, 256>(a);
+        else if (fused_variant() == 6) rc = launch_cost_vec<T, Model, 64>(a);
+        else
+#endif
+        if (vec_family<T>()) rc = launch_cost_vec<T, Model, 64>(a);
         if (rc == 1) rc = launch_cost_staged<T, Model, 128, 2>(a);
         if (rc <= 0) return rc;
       }
@@ -1532,11 +1548,18 @@ static int run_op(Op op, const ModelArgs& a) {
 
 template <typename T>
 static int run_model(int model, int P, Op op, const ModelArgs& a) {
+#ifdef NLLS_USER_MODEL_HEADER
+  if (model == NLLS_MODEL_USER && P == UserModel<T>::P) return run_op<T, UserModel<T>>(op, a);
+  set_error("plugin library: model id %d / P=%d does not match the compiled functor (id %d, P=%d)", model, P, NLLS_MODEL_USER,
+            UserModel<T>::P);
+  return NLLS_E_MODEL;
+#else
   if (model == NLLS_MODEL_EMG && P == 4) return run_op<T, EmgModel<T>>(op, a);
   if (model == NLLS_MODEL_SKEWGAUSS && P == 4) return run_op<T, SkewGaussModel<T, 4>>(op, a);
   if (model == NLLS_MODEL_SKEWGAUSS && P == 5) return run_op<T, SkewGaussModel<T, 5>>(op, a);
   set_error("unknown model %d with P=%d (EMG: P=4, skewed Gaussian: P=4|5)", model, P);
   return NLLS_E_MODEL;
+#endif
 }
 
 static int dispatch(int model, int dtype, int P, Op op, const ModelArgs& a) {

@@ -221,7 +221,7 @@ def solve(solver, p, function, jac_function, args, wvec, ftol, ptol, gtol, max_i
             sel = torch.zeros(B, dtype=torch.uint8, device=ws.device)
             _lib.call('nlls_model_normal_eq', mid, code, _lib.ptr(work_p), P, _lib.ptr(x), _lib.ptr(y), ybs, ycs,
                       _lib.ptr(ws.w), ws.w.numel(), B, C, N, _lib.ptr(fpp[0]), _lib.ptr(fpp[1]), _lib.ptr(ws.g),
-                      _lib.ptr(ws.H), _lib.ptr(ws.stats), ctrl, st())             # iteration 0: f(p0) -> fpp[0], sel == 0
+                      _lib.ptr(ws.H), _lib.ptr(ws.stats), ctrl, st(), lib=model.lib)             # iteration 0: f(p0) -> fpp[0], sel == 0
         while spec and launched < max_iter and not done:
             hp = ws.hist_base_ptr(launched, max_iter)
             group = min(check_every, max_iter - launched, ws.hist_room(launched))
@@ -229,7 +229,7 @@ def solve(solver, p, function, jac_function, args, wvec, ftol, ptol, gtol, max_i
                 lm_solve()
                 _lib.call('nlls_model_lm_trial', mid, code, _lib.ptr(ws.p_trial), P, _lib.ptr(x), _lib.ptr(y), ybs, ycs,
                           _lib.ptr(ws.w), ws.w.numel(), B, C, N, _lib.ptr(fpp[0]), _lib.ptr(fpp[1]), _lib.ptr(sel),
-                          _lib.ptr(g_t), _lib.ptr(H_t), _lib.ptr(stats_t), ctrl, st())
+                          _lib.ptr(g_t), _lib.ptr(H_t), _lib.ptr(stats_t), ctrl, st(), lib=model.lib)
                 _lib.call('nlls_lm_update_spec', code, _lib.ptr(work_p), _lib.ptr(ws.h), _lib.ptr(ws.g), _lib.ptr(ws.H),
                           _lib.ptr(g_t), _lib.ptr(H_t), _lib.ptr(ws.u), _lib.ptr(ws.v), _lib.ptr(ws.stats), _lib.ptr(stats_t),
                           _lib.ptr(sel), meth, float(lm['rho1']), float(lm['rho2']), float(lm['beta']), float(lm['gama']),
@@ -247,15 +247,15 @@ def solve(solver, p, function, jac_function, args, wvec, ftol, ptol, gtol, max_i
                 if solver == GD:
                     _lib.call('nlls_model_normal_eq_gda', mid, code, _lib.ptr(work_p), P, _lib.ptr(x), _lib.ptr(y), ybs, ycs,
                               _lib.ptr(ws.w), ws.w.numel(), B, C, N, _lib.ptr(fpp[0]), _lib.ptr(fpp[1]), _lib.ptr(ws.g),
-                              _lib.ptr(ws.H), _lib.ptr(ws.stats), ctrl, st())
+                              _lib.ptr(ws.H), _lib.ptr(ws.stats), ctrl, st(), lib=model.lib)
                 else:
                     _lib.call('nlls_model_normal_eq', mid, code, _lib.ptr(work_p), P, _lib.ptr(x), _lib.ptr(y), ybs, ycs,
                               _lib.ptr(ws.w), ws.w.numel(), B, C, N, _lib.ptr(fpp[0]), _lib.ptr(fpp[1]), _lib.ptr(ws.g),
-                              _lib.ptr(ws.H), _lib.ptr(ws.stats), ctrl, st())
+                              _lib.ptr(ws.H), _lib.ptr(ws.stats), ctrl, st(), lib=model.lib)
                 if solver == LM:
                     lm_solve()
                     _lib.call('nlls_model_cost_stat', mid, code, _lib.ptr(ws.p_trial), P, _lib.ptr(x), _lib.ptr(y), ybs, ycs,
-                              B, C, N, _lib.ptr(ws.stat_h), ctrl, st())
+                              B, C, N, _lib.ptr(ws.stat_h), ctrl, st(), lib=model.lib)
                 update(hp)
             launched += group
             ws.post_flags()

@@ -23,6 +23,7 @@ class FusedModel:
     """Base: data layout handling shared by all built-in models."""
     model_id = -1
     n_params = ()
+    lib = None            # plugin library of a compiled user model; None = libnlls_b200.so
 
     def __init__(self, n_costs=None):
         # n_costs: number of cost channels when y is [B,N] (one data row shared by all costs, as in
@@ -58,7 +59,7 @@ class FusedModel:
         f = torch.empty((B, C, N), dtype=p.dtype, device=p.device)
         J = torch.empty((B, C, N, P), dtype=p.dtype, device=p.device) if want_jac else None
         _lib.call('nlls_model_eval', self.model_id, _lib.dtype_code(p), _lib.ptr(pc), P, _lib.ptr(x), _lib.ptr(y),
-                  ybs, ycs, B, C, N, _lib.ptr(f), _lib.ptr(J), None, _lib.stream_ptr())
+                  ybs, ycs, B, C, N, _lib.ptr(f), _lib.ptr(J), None, _lib.stream_ptr(), lib=self.lib)
         return f, J
 
     def cost(self, p, x, y):
@@ -81,6 +82,40 @@ class EMGModel(FusedModel):
 class SkewGaussModel(FusedModel):
     model_id = _lib.MODEL_SKEWGAUSS
     n_params = (4, 5)
+
+
+class CompiledModel(FusedModel):
+    """A user-supplied CUDA device functor compiled into a plugin library."""
+    model_id = _lib.MODEL_USER
+
+    def __init__(self, lib, n_params, name, n_costs=None):
+        super().__init__(n_costs)
+        self.lib, self.n_params, self.name = lib, (int(n_params),), name
+
+    def __repr__(self):
+        return f'CompiledModel({self.name!r}, P={self.n_params[0]})'
+
+
+def compile_model(source, name='user', n_costs=None):
+    """Compile a model written as a CUDA device functor and return it as a fused model object.
+
+    ``source`` is CUDA C++ defining ``template <typename T> struct UserModel`` in namespace ``nlls`` with
+    ``static constexpr int P`` (<= 6 parameters), ``load(const T* p)``, ``T value(T x) const`` and
+    ``void eval(T x, T& m, T (&k)[P]) const`` with ``k = -dm/dp`` (see torchimize_b200/user_models/gauss_offset.cuh;
+    every helper of csrc/models.cuh is in scope).  The cost is the squared error used as residual, as for the
+    built-in models.  nvcc compiles csrc/fused_models.cu for that functor (sm_100a only, ~1 min once, cached in
+    torchimize_b200/_jit/); the returned object's ``cost`` / ``jac`` go to any of the drop-in solvers, which then
+    run the fused kernels of the plugin: no Jacobian tensor, no Python callable inside the iteration.
+    """
+    so = _lib.build_plugin(source, name)
+    lib = _lib.load_plugin(so)
+    return CompiledModel(lib, lib.nlls_user_model_params(), name, n_costs)
+
+
+def compile_model_file(path, name=None, n_costs=None):
+    import os
+    with open(path) as f:
+        return compile_model(f.read(), name or os.path.splitext(os.path.basename(path))[0], n_costs)
 
 
 def fused_model_of(function, jac_function):
