@@ -248,8 +248,11 @@ def run_ours(args):
     # (torchimize_b200.pipeline.solve_host_batches): every step copies ITS inputs (p0, t, y) from pinned host memory and
     # reads its finals back; the copy of step k+1 runs on a copy stream while step k solves (two device slots).  The
     # timed region holds exactly K copies, K solves and K result reads — the first copy is not hidden.
-    from torchimize_b200.pipeline import solve_host_batches
-    hp0, ht, hy = (x.cpu().pin_memory() for x in (p0, t, y))
+    from torchimize_b200.pipeline import solve_host_batches, host_memory_near
+    with host_memory_near(local) as numa:                        # one process per GPU: pinned buffers on the GPU's NUMA node
+        hp0, ht = p0.cpu().pin_memory(), t.cpu().pin_memory()
+        hy = torch.empty(y.shape, dtype=y.dtype).pin_memory()    # first touched (by the copy below) under the policy
+        hy.copy_(y)
     e2e_iters = []
 
     def run_e2e(steps):
@@ -321,6 +324,7 @@ def run_ours(args):
                            'parallelism': f'B sharded over {world} GPU(s), no per-iteration collective, one all-gather of finals'},
                 'e2e': {'value': e2e_val, 'unit': UNIT, 'h2d_bytes_per_step': h2d, 'd2h_bytes_per_step': d2h,
                         'ms_per_step': ms_e2e / e2e_steps, 'steps': e2e_steps,
+                        'host_numa_node': numa.node, 'host_numa_policy_set': numa.ok,
                         'api': 'torchimize_b200.pipeline.solve_host_batches (double-buffered H2D on a copy stream; K copies + '
                                'K solves + K result reads inside the timed region)'},
                 'gpu_launches': launches, 'roofline': roof, 'clocks': sampler.summary()}

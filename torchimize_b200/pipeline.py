@@ -109,3 +109,60 @@ def solve_host_batches(solver, batches, function, jac_function=None, wvec=None, 
             enqueue_copy()
         s.free.synchronize()
         yield s.out, len(coeffs)
+
+
+# ------------------------------------------------------------------------------------ host memory placement
+def numa_node_of_gpu(index):
+    """NUMA node the GPU's PCIe root hangs off (sysfs), or None when it cannot be determined."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        bus = pynvml.nvmlDeviceGetPciInfo(pynvml.nvmlDeviceGetHandleByIndex(index)).busId
+        bus = bus.decode() if isinstance(bus, bytes) else bus
+        dom, rest = bus.split(':', 1)
+        with open(f'/sys/bus/pci/devices/{dom[-4:].lower()}:{rest.lower()}/numa_node') as f:
+            node = int(f.read())
+        return node if node >= 0 else None
+    except Exception:                                             # noqa: BLE001
+        return None
+
+
+class host_memory_near:
+    """Context manager: pinned buffers allocated inside it are placed on the NUMA node of GPU ``index``
+    (set_mempolicy(MPOL_PREFERRED) on the calling thread, which the pinned-memory allocation inherits), so that
+    with one process per GPU every rank's host->device copies read node-local memory instead of all ranks
+    pulling from the node the launcher happened to start on.  Best effort: a no-op when the node is unknown or
+    the call is not permitted; ``.node`` / ``.ok`` say what happened."""
+    _SYS_SET_MEMPOLICY = {'x86_64': 238, 'aarch64': 237}
+
+    def __init__(self, index):
+        self.node, self.ok = numa_node_of_gpu(index), False
+
+    def _policy(self, mode, node):
+        import ctypes
+        import platform
+        nr = self._SYS_SET_MEMPOLICY.get(platform.machine())
+        if nr is None:
+            return False
+        libc = ctypes.CDLL(None, use_errno=True)
+        if node is None:
+            return libc.syscall(nr, mode, None, 0) == 0
+        mask = (ctypes.c_ulong * 4)()
+        mask[node // 64] = 1 << (node % 64)
+        return libc.syscall(nr, mode, mask, 4 * 64 + 1) == 0
+
+    def __enter__(self):
+        if self.node is not None:
+            try:
+                self.ok = self._policy(1, self.node)              # MPOL_PREFERRED
+            except Exception:                                     # noqa: BLE001
+                self.ok = False
+        return self
+
+    def __exit__(self, *exc):
+        if self.ok:
+            try:
+                self._policy(0, None)                             # MPOL_DEFAULT
+            except Exception:                                     # noqa: BLE001
+                pass
+        return False
