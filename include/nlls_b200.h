@@ -43,6 +43,7 @@ enum {                       /* negative return codes */
 enum { NLLS_SOLVER_GN = 0, NLLS_SOLVER_LM = 1, NLLS_SOLVER_GD = 2 };
 enum { NLLS_LM_LEVENBERG = 0, NLLS_LM_MARQUARDT = 1 };
 enum { NLLS_MODEL_EMG = 0, NLLS_MODEL_SKEWGAUSS = 1,
+       NLLS_MODEL_MULTI_EMG = 2 /* sum of 2..4 EMG peaks (P = 8|12|16): nlls_model_eval only */,
        NLLS_MODEL_USER = 100 /* the functor a plugin library was compiled for (torchimize_b200.models.compile_model) */ };
 
 /* Device-resident iteration control block (48 bytes, 8-byte aligned, zero-initialise).

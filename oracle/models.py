@@ -155,3 +155,46 @@ def gauss_offset_jac(p, x, y, n_costs=None):
     if n_costs is not None and J.shape[1] == 1:
         J = J.expand(-1, n_costs, -1, -1).contiguous()
     return J
+
+
+# ----------------------------------------------------------------------- sum of K EMG peaks
+# SURVEY.md §8d large-P workload (cfg-4: 4 peaks = 16 parameters): the reference's EMG model and partials
+# (tests/emg.py:19-49) applied per peak; model values summed in peak order, Jacobian blocks concatenated.
+def multi_emg_model(p, t):
+    K = p.shape[1] // 4
+    m = emg_model(p[:, :4], t)
+    for j in range(1, K):
+        m = m + emg_model(p[:, 4 * j:4 * j + 4], t)
+    return m
+
+
+def multi_emg_cost(p, t, y, n_costs=None):
+    f = (_as_bcn(y, p) - multi_emg_model(p, t)[:, None, :]) ** 2
+    if n_costs is not None and f.shape[1] == 1:
+        f = f.expand(-1, n_costs, -1).contiguous()
+    return f
+
+
+def multi_emg_jac(p, t, y, n_costs=None):
+    K = p.shape[1] // 4
+    yb = _as_bcn(y, p)
+    c = 2 * (yb - multi_emg_model(p, t)[:, None, :])                                 # [B,C,N]
+    blocks = []
+    for j in range(K):
+        pj = p[:, 4 * j:4 * j + 4]
+        # emg_jac(pj, t, y_j) = 2 (y_j - m_j) * dm_j: with y_j := m_j + 1/2 the factor is exactly 1 -> dm_j [B,1,N,4]
+        alpha, mu, sigma, eta = _cols(pj)
+        d = t - mu
+        G, A, E = emg_terms(pj, t)
+        dA_mu = E * -1 * _SQRT_2_OVER_PI * eta / sigma
+        dA_sigma = E * -1 * _SQRT_2_OVER_PI * eta * d / sigma ** 2
+        dA_eta = E * _SQRT_2_OVER_PI * d / sigma
+        dG_mu = G * d / sigma ** 2
+        dG_sigma = G * d ** 2 / sigma ** 3
+        blocks.append(torch.stack([-1 * G * A, alpha * (-1 * (G * dA_mu + dG_mu * A)), alpha * (-1 * (G * dA_sigma + dG_sigma * A)),
+                                   alpha * (-1 * G * dA_eta)], dim=-1))
+    dm = torch.cat(blocks, dim=-1)                                                   # [B,N,4K]
+    J = c[..., None] * dm[:, None, :, :]
+    if n_costs is not None and J.shape[1] == 1:
+        J = J.expand(-1, n_costs, -1, -1).contiguous()
+    return J

@@ -122,14 +122,15 @@ def lma(p, function, jac_function=None, args=(), wvec=None, ftol=1e-8, ptol=1e-8
     fun, jac = _bind(function, jac_function, args)
     assert p.dim() == 2
     B, P = p.shape
-    wvec = torch.ones(1, dtype=p.dtype) if wvec is None else wvec
-    dscale = torch.ones(B, dtype=p.dtype)          # D is always dscale * I  (lma:77,84,88)
-    eye = torch.eye(P, dtype=p.dtype)[None]
-    u = tau * torch.ones(B, dtype=p.dtype)         # Q8
-    v = 2 * torch.ones(B, dtype=p.dtype)
-    inf2 = torch.tensor([-torch.inf, torch.inf], dtype=p.dtype)
+    wvec = torch.ones(1, dtype=p.dtype, device=p.device) if wvec is None else wvec
+    kw = dict(dtype=p.dtype, device=p.device)      # reference: every state tensor lives on p.device (lma:76-79)
+    dscale = torch.ones(B, **kw)                   # D is always dscale * I  (lma:77,84,88)
+    eye = torch.eye(P, **kw)[None]
+    u = tau * torch.ones(B, **kw)                  # Q8
+    v = 2 * torch.ones(B, **kw)
+    inf2 = torch.tensor([-torch.inf, torch.inf], **kw)
     tr = Trace()
-    f_prev = torch.zeros(1, dtype=p.dtype)
+    f_prev = torch.zeros(1, dtype=p.dtype, device=p.device)
     while tr.iterations < max_iter:
         f, J = fun(p), jac(p)
         g, H = normal_equations(f, J, wvec)
@@ -168,9 +169,9 @@ def gna(p, function, jac_function=None, args=(), wvec=None, ftol=1e-8, ptol=1e-8
     The reference hands ``l`` to an unused positional slot, so the step rate is always 1 (Q4)."""
     fun, jac = _bind(function, jac_function, args)
     assert p.dim() == 2
-    wvec = torch.ones(1, dtype=p.dtype) if wvec is None else wvec
+    wvec = torch.ones(1, dtype=p.dtype, device=p.device) if wvec is None else wvec
     tr = Trace()
-    f_prev = torch.zeros(1, dtype=p.dtype)
+    f_prev = torch.zeros(1, dtype=p.dtype, device=p.device)
     while tr.iterations < max_iter:
         f, J = fun(p), jac(p)
         g, H = normal_equations(f, J, wvec)
@@ -212,9 +213,9 @@ def gda(p, function, jac_function=None, args=(), wvec=None, ftol=1e-8, ptol=1e-8
     reference: gda_fun_parallel.py:23-87.  fcon is batch-global (Q5)."""
     fun, jac = _bind(function, jac_function, args)
     assert p.dim() == 2
-    wvec = torch.ones(1, dtype=p.dtype) if wvec is None else wvec
+    wvec = torch.ones(1, dtype=p.dtype, device=p.device) if wvec is None else wvec
     tr = Trace()
-    f_prev = torch.zeros(1, dtype=p.dtype)
+    f_prev = torch.zeros(1, dtype=p.dtype, device=p.device)
     while tr.iterations < max_iter:
         f, h = gda_step(p, fun, jac, wvec, l)
         g = h / l

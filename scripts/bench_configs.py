@@ -2,7 +2,7 @@
 """Secondary measurements (not the bench.py contract): every BASELINE.json config shape that fits
 one GPU, per-kernel CUDA-event times and achieved algorithmic GB/s.  One JSON line per case.
 
-    python scripts/bench_configs.py [case ...]     cases: cfg2-gn cfg2-lm cfg2-gd cfg2-gn-f32 cfg3-gd cfg3-lm cfg4-k1
+    python scripts/bench_configs.py [case ...]     cases: cfg2-gn cfg2-lm cfg2-gd cfg2-gn-f32 cfg3-gd cfg3-lm cfg4-k1 cfg4-lm cfg4-gn
 """
 import json
 import os
@@ -14,7 +14,7 @@ import torch                                                        # noqa: E402
 from bench import make_batch                                        # noqa: E402
 from torchimize_b200 import _lib                                    # noqa: E402
 from torchimize_b200.functions import lsq_gna_parallel, lsq_lma_parallel, gradient_descent_parallel   # noqa: E402
-from torchimize_b200.models import EMGModel, SkewGaussModel         # noqa: E402
+from torchimize_b200.models import EMGModel, SkewGaussModel, MultiEMGModel   # noqa: E402
 
 DEV = 'cuda'
 PEAK = float(json.load(open(os.path.join(ROOT, 'MEASURED_PEAKS.json'))).get('hbm_gbs', 6650.0)) if os.path.exists(
@@ -106,6 +106,42 @@ def case_cfg3(kind, P=5):
     report(f'cfg3-{kind}-P{P}', B, ms, iters, kern, bytes_of)
 
 
+def multi_emg_batch(B, K, N, dt, seed=3010):
+    """cfg-4 end to end: sum of K EMG peaks, centres spread over t, 16 parameters for K = 4."""
+    g = torch.Generator(device=DEV).manual_seed(seed)
+    t = torch.linspace(-1e3, 1e3, N, device=DEV).double()
+    centres = torch.linspace(-600, 600, K, dtype=torch.float64, device=DEV)
+    base = torch.stack([torch.tensor([10., 0., 60., 3.], dtype=torch.float64, device=DEV) +
+                        torch.tensor([0., 1., 0., 0.], dtype=torch.float64, device=DEV) * c for c in centres]).reshape(-1)
+    scale = base.abs().clamp(min=20.)
+    gt = base + scale * .05 * (torch.rand(B, 4 * K, generator=g, dtype=torch.float64, device=DEV) - .5)
+    p0 = gt + scale * .04 * (torch.rand(B, 4 * K, generator=g, dtype=torch.float64, device=DEV) - .5)
+    y = torch.empty(B, 1, N, dtype=dt, device=DEV)
+    for b0 in range(0, B, 4096):
+        q = gt[b0:b0 + 4096]
+        m = 0
+        for j in range(K):
+            a, mu, sg, eta = (q[:, 4 * j + i, None] for i in range(4))
+            d = t - mu
+            m = m + a * torch.exp(-.5 * d ** 2 / sg ** 2) * (1 + torch.erf(eta * d / (sg * 2 ** .5)))
+        y[b0:b0 + 4096, 0] = (m + .01 * torch.randn(m.shape, generator=g, dtype=torch.float64, device=DEV)).to(dt)
+    return p0.to(dt), t.to(dt), y, gt
+
+
+def case_cfg4(kind):
+    """cfg-4 end to end: lsq_lma_parallel / lsq_gna_parallel on B=32768 four-peak EMG fits, C=1, N=4096, P=16, fp64,
+    tensor path: nlls_model_eval materialises f and J, K1 (DMMA) reduces them, K2 (warp Cholesky) solves."""
+    B, C, N, K = 32768, 1, 4096, 4
+    P, dt, s = 4 * K, torch.float64, 8
+    p0, t, y, gt = multi_emg_batch(B, K, N, dt)
+    w = torch.ones(C, dtype=dt, device=DEV)
+    kw = dict(meth='lev') if kind == 'lm' else {}
+    ms, iters, kern = timed_solve(SOLVERS[kind], p0, MultiEMGModel(K), (t, y), w, 40, reps=2, **kw)
+    bytes_of = {'nlls_normal_eq': s * C * N * (P + 2) * B, 'nlls_cost_stat': s * C * N * B}
+    # nlls_model_eval is called for f alone, for J (+f) and, in LM, for the trial cost: report its average only
+    report(f'cfg4-{kind}', B, ms, iters, kern, bytes_of)
+
+
 def case_cfg4_k1():
     """Kernel-level: K1 (wide, P=16) + K2 on seeded N(0,1) tensors of the cfg-4 shape."""
     B, C, N, P = 32768, 1, 4096, 16
@@ -154,7 +190,7 @@ def case_cfg4_k1():
 CASES = {'cfg2-gn': lambda: case_cfg2('gn'), 'cfg2-lm': lambda: case_cfg2('lm'), 'cfg2-gd': lambda: case_cfg2('gd'),
          'cfg2-gn-f32': lambda: case_cfg2('gn', 'f32'), 'cfg2-lm-f32': lambda: case_cfg2('lm', 'f32'),
          'cfg3-gd': lambda: case_cfg3('gd'), 'cfg3-lm': lambda: case_cfg3('lm'), 'cfg3-gn': lambda: case_cfg3('gn'),
-         'cfg4-k1': case_cfg4_k1}
+         'cfg4-k1': case_cfg4_k1, 'cfg4-lm': lambda: case_cfg4('lm'), 'cfg4-gn': lambda: case_cfg4('gn')}
 
 if __name__ == '__main__':
     assert _lib.load().nlls_device_check() == 0

@@ -1,0 +1,59 @@
+"""The torch-on-GPU bar: the reference's own torch-op sequence (the oracle port,
+which test_oracle_golden.py pins to the reference bit for bit) run with device='cuda' on the same B200, same seeded
+inputs, against this package's kernels.  Checks parity on that CUDA run too and records both times."""
+import json
+import os
+import time
+
+import pytest
+import torch
+
+from conftest import ROOT
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize('solver', ['gna', 'lma'])
+def test_kernels_beat_the_reference_torch_ops_on_the_same_gpu(solver):
+    from bench import make_batch
+    from oracle import nlls_oracle as O, models as M
+    from torchimize_b200.functions import lsq_gna_parallel, lsq_lma_parallel
+    from torchimize_b200.models import EMGModel
+    dev = torch.device('cuda:0')
+    B, C, N = 8192, 5, 1024                                       # cfg-2 shape at 1/8 of its batch (torch path: J + temporaries)
+    p0, t, y = make_batch(B, C, N, 3008, dev, torch.float64)
+    w = torch.ones(C, dtype=torch.float64, device=dev)
+    kw = dict(ftol=1e-8, ptol=1e-8, gtol=1e-8, max_iter=80 if solver == 'gna' else 40)
+    emg = EMGModel()
+    ours = lsq_gna_parallel if solver == 'gna' else lsq_lma_parallel
+
+    def run_ref():
+        return getattr(O, solver)(p0.clone(), M.emg_cost, M.emg_jac, args=(t, y), wvec=w, **kw)
+
+    def run_ours():
+        p = p0.clone()
+        return p, ours(p, emg.cost, emg.jac, args=(t, y), wvec=w, **kw)
+
+    def wall(fn, reps):
+        fn()
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        for _ in range(reps):
+            out = fn()
+        torch.cuda.synchronize()
+        return (time.perf_counter() - t0) / reps, out
+
+    s_ref, tr = wall(run_ref, 2)
+    s_ours, (p, coeffs) = wall(run_ours, 5)
+    assert len(coeffs) == tr.iterations
+    ref_final = tr.p_list[-1]
+    err = float(((p - ref_final).norm(dim=1) / ref_final.norm(dim=1)).max())
+    assert err <= 1e-9, f'{solver}: rel err {err:.2e} vs the reference torch-op sequence on CUDA'
+    rec = {'solver': solver, 'B': B, 'C': C, 'N': N, 'dtype': 'f64', 'iterations': tr.iterations,
+           'torch_ops_on_b200_s': s_ref, 'kernels_s': s_ours, 'speedup': s_ref / s_ours,
+           'torch_ops_problems_per_s': B / s_ref, 'kernels_problems_per_s': B / s_ours, 'max_rel_err': err}
+    print('TORCH-ON-GPU BAR', json.dumps(rec))
+    out_dir = os.path.join(ROOT, 'gpurun_out')
+    if os.path.isdir(out_dir):
+        with open(os.path.join(out_dir, f'torch_gpu_bar_{solver}.json'), 'w') as f:
+            json.dump(rec, f)
+    assert s_ours * 5 < s_ref, f'kernels {s_ours * 1e3:.1f} ms vs torch ops {s_ref * 1e3:.1f} ms on the same GPU'

@@ -14,7 +14,7 @@ CSRC = os.path.join(_HERE, 'csrc')
 F32, F64 = 0, 1
 SOLVER_GN, SOLVER_LM, SOLVER_GD = 0, 1, 2
 LM_LEVENBERG, LM_MARQUARDT = 0, 1
-MODEL_EMG, MODEL_SKEWGAUSS, MODEL_USER = 0, 1, 100
+MODEL_EMG, MODEL_SKEWGAUSS, MODEL_MULTI_EMG, MODEL_USER = 0, 1, 2, 100
 CTRL_BYTES = 48
 
 _vp, _i, _ll, _d = ctypes.c_void_p, ctypes.c_int, ctypes.c_longlong, ctypes.c_double

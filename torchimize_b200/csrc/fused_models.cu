@@ -32,6 +32,7 @@ constexpr int kFusedS = 4;       // abscissa samples per thread per tile
 
 template <typename T>
 __device__ __forceinline__ T ld_cached(const T* p) { return __ldg(p); }
+__device__ __forceinline__ bool aligned_to_dev(const void* p, size_t a) { return (reinterpret_cast<uintptr_t>(p) % a) == 0; }
 
 // ------------------------------------------------------------------ fused normal equations
 template <typename T, typename Model, int TPB, int S>
@@ -1229,31 +1230,49 @@ k_model_normal_eq_gda_staged(const T* __restrict__ p, const T* __restrict__ x, c
 }
 
 // ------------------------------------------------------------------ materialising callables
-// thread per (b, n): writes f[b,c,n] and J[b,c,n,:] for every cost c.
+// A warp (or `wpp` warps) per problem: the per-problem constants (Model::load: divisions) are computed once per lane and
+// problem, lanes stride over the abscissa; writes f[b,c,n] and J[b,c,n,:] for every cost c.
 template <typename T, typename Model>
 __global__ void __launch_bounds__(256)
 k_model_eval(const T* __restrict__ p, const T* __restrict__ x, const T* __restrict__ y, long long ybs, long long ycs,
-             long long B, int C, int N, T* __restrict__ f_out, T* __restrict__ J_out, const nlls_ctrl* ctrl) {
+             long long B, int C, int N, T* __restrict__ f_out, T* __restrict__ J_out, const nlls_ctrl* ctrl, int wpp) {
   if (is_done(ctrl)) return;
   constexpr int P = Model::P;
-  const long long total = B * (long long)N;
-  for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
-       idx += (long long)gridDim.x * blockDim.x) {
-    const long long b = idx / N;
-    const int n = (int)(idx - b * N);
+  const int lane = threadIdx.x & 31;
+  const long long nwarps = ((long long)gridDim.x * blockDim.x) >> 5, items = B * (long long)wpp;
+  const bool j16 = J_out != nullptr && aligned_to_dev(J_out, 16);
+  for (long long w = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5; w < items; w += nwarps) {
+    const long long b = w / wpp;
+    const int part = (int)(w - b * wpp);
     Model M;
     M.load(p + b * P);
-    T m, k[P];
-    if (J_out) M.eval(ld_cached(x + n), m, k);
-    else m = M.value(ld_cached(x + n));
-    for (int c = 0; c < C; ++c) {
-      const T r = ld_cached(y + b * ybs + c * ycs + n) - m;
-      const long long row = (b * C + c) * (long long)N + n;
-      f_out[row] = r * r;
-      if (J_out) {
-        const T c2 = T(2) * r;
+    for (int n = part * 32 + lane; n < N; n += 32 * wpp) {
+      T m, k[P];
+      if (J_out) M.eval(ld_cached(x + n), m, k);
+      else m = M.value(ld_cached(x + n));
+      for (int c = 0; c < C; ++c) {
+        const T r = ld_cached(y + b * ybs + c * ycs + n) - m;
+        const long long row = (b * C + c) * (long long)N + n;
+        f_out[row] = r * r;
+        if (J_out) {
+          const T c2 = T(2) * r;
+          T* Jr = J_out + row * P;
+          if constexpr ((P * sizeof(T)) % 16 == 0) {         // rows are 16-byte granular: 128-bit stores
+            if (j16) {
+              constexpr int VEC = Lane16<T>::VEC;
 #pragma unroll
-        for (int i = 0; i < P; ++i) J_out[row * P + i] = c2 * k[i];
+              for (int i = 0; i < P; i += VEC) {
+                T v[VEC];
+#pragma unroll
+                for (int j = 0; j < VEC; ++j) v[j] = c2 * k[i + j];
+                Lane16<T>::stg(Jr + i, v);
+              }
+              continue;
+            }
+          }
+#pragma unroll
+          for (int i = 0; i < P; ++i) Jr[i] = c2 * k[i];
+        }
       }
     }
   }
@@ -1457,6 +1476,21 @@ static int launch_gda_staged(const ModelArgs& a) {
 }
 
 template <typename T, typename Model>
+static int launch_eval(const ModelArgs& a) {
+  auto kern = k_model_eval<T, Model>;
+  const long long target_warps = 148LL * 8 * 8;              // 148 SMs x 8 CTAs x 8 warps
+  long long wpp = a.B >= target_warps ? 1 : (target_warps + a.B - 1) / a.B;   // warps per problem when the batch is small
+  const long long max_wpp = (a.N + 63) / 64;
+  if (wpp > max_wpp) wpp = max_wpp;
+  if (wpp < 1) wpp = 1;
+  long long blocks = (a.B * wpp + 7) / 8;
+  if (blocks > 148LL * 8) blocks = 148LL * 8;
+  kern<<<(int)blocks, 256, 0, a.st>>>((const T*)a.p, (const T*)a.x, (const T*)a.y, a.ybs, a.ycs, a.B, a.C, a.N,
+                                      (T*)a.f_out, (T*)a.J_out, a.ctrl, (int)wpp);
+  return check_launch("nlls_model_eval");
+}
+
+template <typename T, typename Model>
 static int run_op(Op op, const ModelArgs& a) {
   constexpr int TPB = kFusedTPB, S = kFusedS, NW = TPB / 32, P = Model::P, V = P + Tri<P>::N + 2;
   switch (op) {
@@ -1534,15 +1568,16 @@ static int run_op(Op op, const ModelArgs& a) {
                                       a.ctrl);
       return check_launch("nlls_model_cost_stat");
     }
-    case OP_EVAL: {
-      auto kern = k_model_eval<T, Model>;
-      long long blocks = (a.B * (long long)a.N + 255) / 256;
-      if (blocks > 148LL * 8 * 8) blocks = 148LL * 8 * 8;
-      kern<<<(int)blocks, 256, 0, a.st>>>((const T*)a.p, (const T*)a.x, (const T*)a.y, a.ybs, a.ycs, a.B, a.C, a.N,
-                                          (T*)a.f_out, (T*)a.J_out, a.ctrl);
-      return check_launch("nlls_model_eval");
-    }
+    case OP_EVAL: return launch_eval<T, Model>(a);
   }
+  return NLLS_E_MODEL;
+}
+
+// models that only exist on the materialising path (P > 6: the fused kernels keep g and H in registers)
+template <typename T, typename Model>
+static int run_eval_only(Op op, const ModelArgs& a, const char* name) {
+  if (op == OP_EVAL) return launch_eval<T, Model>(a);
+  set_error("%s (P=%d) has no fused normal-equation kernels: use the tensor path (nlls_model_eval + nlls_normal_eq)", name, Model::P);
   return NLLS_E_MODEL;
 }
 
@@ -1557,7 +1592,10 @@ static int run_model(int model, int P, Op op, const ModelArgs& a) {
   if (model == NLLS_MODEL_EMG && P == 4) return run_op<T, EmgModel<T>>(op, a);
   if (model == NLLS_MODEL_SKEWGAUSS && P == 4) return run_op<T, SkewGaussModel<T, 4>>(op, a);
   if (model == NLLS_MODEL_SKEWGAUSS && P == 5) return run_op<T, SkewGaussModel<T, 5>>(op, a);
-  set_error("unknown model %d with P=%d (EMG: P=4, skewed Gaussian: P=4|5)", model, P);
+  if (model == NLLS_MODEL_MULTI_EMG && P == 8) return run_eval_only<T, MultiEmgModel<T, 2>>(op, a, "2-peak EMG");
+  if (model == NLLS_MODEL_MULTI_EMG && P == 12) return run_eval_only<T, MultiEmgModel<T, 3>>(op, a, "3-peak EMG");
+  if (model == NLLS_MODEL_MULTI_EMG && P == 16) return run_eval_only<T, MultiEmgModel<T, 4>>(op, a, "4-peak EMG");
+  set_error("unknown model %d with P=%d (EMG: P=4, skewed Gaussian: P=4|5, multi-peak EMG: P=8|12|16)", model, P);
   return NLLS_E_MODEL;
 #endif
 }

@@ -111,6 +111,35 @@ struct EmgModel {
   }
 };
 
+// Sum of K EMG peaks, p = [alpha_1, mu_1, sigma_1, eta_1, ..., alpha_K, mu_K, sigma_K, eta_K] (the
+// large-P workload of cfg-4, 4 peaks = 16 parameters).  Values are summed in peak order; the derivative block of peak
+// j is EmgModel's.  Used by the materialising kernel only (nlls_model_eval -> K1 on the fp64 tensor cores for P > 8).
+template <typename T, int K>
+struct MultiEmgModel {
+  static constexpr int P = 4 * K;
+  EmgModel<T> peak[K];
+  __device__ __forceinline__ void load(const T* __restrict__ p) {
+#pragma unroll
+    for (int j = 0; j < K; ++j) peak[j].load(p + 4 * j);
+  }
+  __device__ __forceinline__ T value(T t) const {
+    T m = peak[0].value(t);
+#pragma unroll
+    for (int j = 1; j < K; ++j) m += peak[j].value(t);
+    return m;
+  }
+  __device__ __forceinline__ void eval(T t, T& m, T (&k)[P]) const {
+#pragma unroll
+    for (int j = 0; j < K; ++j) {
+      T mj, kj[4];
+      peak[j].eval(t, mj, kj);
+      m = j == 0 ? mj : m + mj;
+#pragma unroll
+      for (int i = 0; i < 4; ++i) k[4 * j + i] = kj[i];
+    }
+  }
+};
+
 template <typename T, int NP>
 struct SkewGaussModel {
   static constexpr int P = NP;                                // 4, or 5 with a constant offset

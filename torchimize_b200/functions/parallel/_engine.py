@@ -18,7 +18,7 @@ import warnings
 import torch
 
 from ... import _lib
-from ...models import fused_model_of
+from ...models import fused_model_of, model_owner_of
 from ..jacobian import batch_jacobian_approx_t
 
 GN, LM, GD = _lib.SOLVER_GN, _lib.SOLVER_LM, _lib.SOLVER_GD
@@ -264,14 +264,20 @@ def solve(solver, p, function, jac_function, args, wvec, ftol, ptol, gtol, max_i
     else:
         # ----------------------------------------------------------------- tensor path
         fun, jac = bind_callables(function, jac_function, args)
+        owner = model_owner_of(function, jac_function)      # built-in / compiled model on the tensor path: one eval launch
         f_prev = None
         iters, sing = 0, 0
         for k in range(max_iter):
-            f = _as_work(fun(work_p), ws.dtype, 'function')
-            if f.dim() != 3 or f.shape[0] != B:
-                raise _lib.NllsError(f'function must return [B,C,N] residuals, got {tuple(f.shape)}')
+            if owner is not None:
+                f, J = owner.cost_and_jac(work_p, *args)
+            else:
+                f = _as_work(fun(work_p), ws.dtype, 'function')
+                if f.dim() != 3 or f.shape[0] != B:
+                    raise _lib.NllsError(f'function must return [B,C,N] residuals, got {tuple(f.shape)}')
+                J = None
             _, C, N = f.shape
-            J = _as_work(jac(work_p), ws.dtype, 'jac_function', (B, C, N, P))
+            if J is None:
+                J = _as_work(jac(work_p), ws.dtype, 'jac_function', (B, C, N, P))
             if ws.w.numel() not in (1, C):
                 raise _lib.NllsError(f'wvec has {ws.w.numel()} entries for {C} costs')
             hp = ws.hist_base_ptr(k, max_iter)

@@ -24,6 +24,7 @@ class FusedModel:
     model_id = -1
     n_params = ()
     lib = None            # plugin library of a compiled user model; None = libnlls_b200.so
+    fused_ops = True      # False: only the materialising kernel exists (solvers take the tensor path)
 
     def __init__(self, n_costs=None):
         # n_costs: number of cost channels when y is [B,N] (one data row shared by all costs, as in
@@ -84,6 +85,20 @@ class SkewGaussModel(FusedModel):
     n_params = (4, 5)
 
 
+class MultiEMGModel(FusedModel):
+    """Sum of ``n_peaks`` (2..4) EMG peaks, p = [alpha_1, mu_1, sigma_1, eta_1, ...] (P = 4 n_peaks; SURVEY.md §8d, the
+    large-P workload of cfg-4).  Residuals and Jacobian are materialised by ``nlls_model_eval``; the solvers then run
+    the tensor path, whose normal equations go to the fp64 tensor cores for P > 8."""
+    model_id = _lib.MODEL_MULTI_EMG
+    fused_ops = False
+
+    def __init__(self, n_peaks=4, n_costs=None):
+        super().__init__(n_costs)
+        if n_peaks not in (2, 3, 4):
+            raise _lib.NllsError('MultiEMGModel: n_peaks must be 2, 3 or 4')
+        self.n_params = (4 * n_peaks,)
+
+
 class CompiledModel(FusedModel):
     """A user-supplied CUDA device functor compiled into a plugin library."""
     model_id = _lib.MODEL_USER
@@ -118,10 +133,21 @@ def compile_model_file(path, name=None, n_costs=None):
         return compile_model(f.read(), name or os.path.splitext(os.path.basename(path))[0], n_costs)
 
 
+def model_owner_of(function, jac_function):
+    """The FusedModel whose bound ``cost`` / ``jac`` the two callables are (fused kernels or not), else None: lets the
+    tensor path evaluate residuals and Jacobian with ONE nlls_model_eval launch instead of two."""
+    owner = getattr(function, '__self__', None)
+    if not isinstance(owner, FusedModel) or getattr(function, '__func__', None) is not FusedModel.cost:
+        return None
+    if getattr(jac_function, '__self__', None) is owner and getattr(jac_function, '__func__', None) is FusedModel.jac:
+        return owner
+    return None
+
+
 def fused_model_of(function, jac_function):
     """The FusedModel both callables belong to, else None (=> tensor path)."""
     owner = getattr(function, '__self__', None)
-    if not isinstance(owner, FusedModel) or getattr(function, '__func__', None) is not FusedModel.cost:
+    if not isinstance(owner, FusedModel) or getattr(function, '__func__', None) is not FusedModel.cost or not owner.fused_ops:
         return None
     if jac_function is None:
         return owner          # analytic Jacobian of the built-in model stands in for autograd's
