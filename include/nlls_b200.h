@@ -136,6 +136,13 @@ int nlls_gd_update(int dtype, void* p, const double* g64, const double* H64, con
  * multi-GPU exact run).  */
 int nlls_iter_end(nlls_ctrl* ctrl, int solver, double ftol, void* stream);
 
+/* ---- single-problem solvers (torchimize/functions/single/*.py: lma_fun_single.py:81,99; gna:81; gda:78) ----------
+ * Residual statistics of ONE problem over a vector of any length, spread over the whole GPU: block k writes
+ * out[2k] = partial sum_i a[i]^2 and out[2k+1] = partial sum_i (b[i]-a[i])^2 (0 when b is NULL), fp64;
+ * out holds 2 * nlls_sumsq_partials() doubles, the caller adds the partials (fixed order: deterministic). */
+int nlls_sumsq_partials(void);
+int nlls_sumsq(int dtype, const void* a, const void* b /*nullable*/, long long n, double* out, void* stream);
+
 /* ---- K4: fused built-in models (tests/emg.py:19-49, tests/unit_test_parallel.py:81-118;
  *          tests/unit_test_skewed_gaussian.py:43-51) ------------------------------------
  * Data layout: x [N] shared abscissa, y [B,*,N] with strides (y_bstride, y_cstride) in

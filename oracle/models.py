@@ -198,3 +198,13 @@ def multi_emg_jac(p, t, y, n_costs=None):
     if n_costs is not None and J.shape[1] == 1:
         J = J.expand(-1, n_costs, -1, -1).contiguous()
     return J
+
+
+# ------------------------------------------------------------- single-problem EMG callables
+# tests/unit_test_analytical_jacobian.py:35,50-73: p [4], t [N], y [N] -> f [N] = (y - emg(p, t))^2, J [N,4].
+def emg_single_cost(p, t, y):
+    return emg_cost(p[None], t, y[None])[0, 0]
+
+
+def emg_single_jac(p, t, y):
+    return emg_jac(p[None], t, y[None])[0, 0]

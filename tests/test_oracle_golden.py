@@ -1,8 +1,12 @@
 """CPU: pins the oracle (oracle/nlls_oracle.py, oracle/models.py) to golden vectors produced by
 the unmodified reference (tests/golden/make_golden.py)."""
+import os
+
+import numpy as np
 import pytest
 import torch
 
+from conftest import GOLDEN
 from helpers import CASES, PLAIN, DT, CHAOTIC_PREFIX, load, compare_plist, rel_err
 from oracle import nlls_oracle as O
 from oracle import models as M
@@ -169,3 +173,43 @@ def test_gda_synthetic_is_chaotic(synthetic, monkeypatch):
     assert got.shape[0] == want.shape[0] == kw['max_iter']
     assert rel_err(got[:CHAOTIC_PREFIX], want[:CHAOTIC_PREFIX]) <= 1e-9
     assert rel_err(got[-1], want[-1]) > 1e-5
+
+
+# ------------------------------------------------------------------ single-problem solvers
+SINGLE_CASES = {
+    'lma_lev': ('lsq_lma', dict(meth='lev', gtol=1e-6, max_iter=39)),
+    'lma_marq': ('lsq_lma', dict(meth='marq', gtol=1e-6, max_iter=39)),
+    'gna': ('lsq_gna', dict(l=.1, gtol=1e-6, max_iter=199)),
+    'gna_l025': ('lsq_gna', dict(l=.25, max_iter=99)),
+    'gda': ('gradient_descent', dict(l=.1, gtol=1e-6, max_iter=199)),
+    'gda_l025': ('gradient_descent', dict(l=.25, max_iter=99)),
+}
+
+
+@pytest.mark.parametrize('dn', ['f64', 'f32'])
+@pytest.mark.parametrize('name', sorted(SINGLE_CASES))
+def test_single_oracle_reproduces_the_reference_trajectories(name, dn):
+    """oracle/single_oracle.py against tests/golden/single.npz (p_lists of the imported reference).  The reference's
+    matmul reductions are multi-threaded, so two runs of the reference itself differ in the last digits: the
+    trajectories are held to 1e-10 (fp64) / 2e-5 (fp32) with identical lengths instead of bit equality."""
+    from oracle import single_oracle as S, models as M
+    gold = dict(np.load(os.path.join(GOLDEN, 'single.npz')))
+    dt = torch.float64 if dn == 'f64' else torch.float32
+    t = torch.as_tensor(gold['t']).to(dt)
+    y, p0 = torch.as_tensor(gold['y']).to(dt), torch.as_tensor(gold['p0']).to(dt)
+    fn, kw = SINGLE_CASES[name]
+    jacs = [('ana', M.emg_single_jac)] + ([('auto', None)] if f'{name}__{dn}__auto' in gold else [])
+    for jn, jac in jacs:
+        want = torch.as_tensor(gold[f'{name}__{dn}__{jn}'])
+        got = torch.stack([q.detach() for q in getattr(S, fn)(p0.clone(), M.emg_single_cost, jac, args=(t, y), **kw)])
+        if dn == 'f32' and fn == 'lsq_lma':
+            # fp32 LM accept/reject decisions sit on rounding noise: two runs of the REFERENCE itself give different
+            # iteration counts (37 vs 39 iterates for 'marq' in two generator runs) — finals only, count reported
+            if got.shape != want.shape:
+                print(f'BOUNDARY FLIP {name} {dn}: {got.shape[0]} iterates, reference {want.shape[0]}')
+            err = float((got[-1] - want[-1]).norm() / want[-1].norm())
+            assert err <= 1e-4, f'{name} {dn} {jn}: final {err:.2e}'
+            continue
+        assert got.shape == want.shape, f'{name} {dn} {jn}: {got.shape[0]} iterates, reference {want.shape[0]}'
+        err = float(((got - want).norm(dim=1) / want.norm(dim=1)).max())
+        assert err <= ((1e-10 if jn == 'ana' else 1e-9) if dn == 'f64' else 2e-5), f'{name} {dn} {jn}: {err:.2e}'

@@ -716,6 +716,46 @@ extern "C" int nlls_gd_update(int dtype, void* p, const double* g64, const doubl
   return 0;
 }
 
+// ---------------------------------------------------------------------------- residual statistics of ONE problem
+// Single-problem solvers (functions/single/*): sums over a residual vector of any length, spread over the whole GPU.
+// Block k writes out[2k] = partial sum of a^2 and out[2k+1] = partial sum of (b - a)^2 (0 when b is NULL) in fp64;
+// fixed grid and fixed per-block order: the host adds the kSumsqBlocks partials, so the result is deterministic.
+constexpr int kSumsqBlocks = 1184, kSumsqTPB = 256;     // 148 SMs x 8
+
+template <typename T>
+__global__ void __launch_bounds__(kSumsqTPB)
+k_sumsq(const T* __restrict__ a, const T* __restrict__ b, long long n, double* __restrict__ out) {
+  double s0 = 0.0, s1 = 0.0;
+  for (long long i = (long long)blockIdx.x * kSumsqTPB + threadIdx.x; i < n; i += (long long)kSumsqBlocks * kSumsqTPB) {
+    const double x = (double)a[i];
+    s0 = fma(x, x, s0);
+    if (b) { const double d = (double)(T)(b[i] - a[i]); s1 = fma(d, d, s1); }   // difference rounded in T like the reference
+  }
+  s0 = warp_sum(s0);
+  s1 = warp_sum(s1);
+  __shared__ double red[2][kSumsqTPB / 32];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  if (lane == 0) { red[0][warp] = s0; red[1][warp] = s1; }
+  __syncthreads();
+  if (threadIdx.x < 2) {
+    double t = 0.0;
+#pragma unroll
+    for (int k = 0; k < kSumsqTPB / 32; ++k) t += red[threadIdx.x][k];
+    out[2 * blockIdx.x + threadIdx.x] = t;
+  }
+}
+
+extern "C" int nlls_sumsq_partials(void) { return kSumsqBlocks; }
+
+extern "C" int nlls_sumsq(int dtype, const void* a, const void* b, long long n, double* out, void* stream) {
+  if (dtype != NLLS_F32 && dtype != NLLS_F64) { set_error("dtype %d is not NLLS_F32/NLLS_F64", dtype); return NLLS_E_DTYPE; }
+  if (n < 0) { set_error("nlls_sumsq: n=%lld", n); return NLLS_E_SHAPE; }
+  if (!a || !out) { set_error("nlls_sumsq: NULL tensor"); return NLLS_E_NULL; }
+  if (dtype == NLLS_F64) k_sumsq<double><<<kSumsqBlocks, kSumsqTPB, 0, (cudaStream_t)stream>>>((const double*)a, (const double*)b, n, out);
+  else k_sumsq<float><<<kSumsqBlocks, kSumsqTPB, 0, (cudaStream_t)stream>>>((const float*)a, (const float*)b, n, out);
+  return check_launch("nlls_sumsq");
+}
+
 extern "C" int nlls_iter_end(nlls_ctrl* ctrl, int solver, double ftol, void* stream) {
   if (!ctrl) { set_error("nlls_iter_end: NULL ctrl"); return NLLS_E_NULL; }
   k_iter_end<<<1, 1, 0, (cudaStream_t)stream>>>(ctrl, solver, ftol);

@@ -1,5 +1,7 @@
-"""Drop-in surface of the batched path: same names as torchimize/functions/__init__.py:4-8.
-(The single-problem solvers of torchimize.functions.single are out of scope — SURVEY.md §8f.)"""
+"""Drop-in surface: same names as torchimize/functions/__init__.py:1-8 (single-problem solvers: SURVEY.md §8f rank 3)."""
+from .single.gda_fun_single import gradient_descent
+from .single.gna_fun_single import lsq_gna
+from .single.lma_fun_single import lsq_lma
 from .parallel.gda_fun_parallel import gradient_descent_parallel, gradient_descent_parallel_plain
 from .parallel.gna_fun_parallel import lsq_gna_parallel, lsq_gna_parallel_plain
 from .parallel.lma_fun_parallel import lsq_lma_parallel
