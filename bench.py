@@ -244,6 +244,36 @@ def run_ours(args):
     launches = _lib.launches - launches0
     iters = iters_seen[-1]
 
+    # ---- the same batch through lsq_lma_parallel meth='lev' (BASELINE.json's metric is quoted for LM and GN): reported
+    # beside the headline GN line, same timing rules (resident inputs, CUDA events, per-launch kernel times)
+    from torchimize_b200.functions import lsq_lma_parallel
+    lm_iters = []
+
+    def step_lm():
+        p.copy_(p0)
+        coeffs = lsq_lma_parallel(p, emg.cost, emg.jac, args=(t, y), wvec=w, ftol=tol, ptol=tol, gtol=tol, meth='lev',
+                                  max_iter=40, fused=fused)
+        lm_iters.append(len(coeffs))
+        return coeffs
+
+    lm_steps = max(1, min(args.steps, 3))
+    for _ in range(2):
+        step_lm()
+    _lib.enable_timing(True)
+    ms_lm, _ = timed(step_lm, lm_steps)
+    lm_recs = _lib.timing_records()
+    _lib.enable_timing(False)
+    lm_per = {}
+    for name, ms in lm_recs:
+        lm_per.setdefault(name, []).append(ms)
+    lm_top = max(lm_per, key=lambda k: sum(lm_per[k]))
+    lm_live = [v for v in lm_per[lm_top] if v > .05 * max(lm_per[lm_top])]
+    lm_avg = sum(lm_live) / len(lm_live)
+    lm_bytes = (3 * esz * C * N if fused else esz * C * N * (P + 3)) * B    # fused: y + f_cur + f_trial; tensor: SURVEY 8d LMA
+    also_lm = {'solver': "lsq_lma_parallel meth='lev', max_iter 40, same batch", 'ms_per_step': ms_lm / lm_steps, 'steps': lm_steps,
+               'iterations': lm_iters[-1], 'kernel': lm_top, 'avg_launch_ms': lm_avg,
+               'achieved_GBps': lm_bytes / (lm_avg * 1e-3) / 1e9}
+
     # ---- end-to-end steps: host buffers in, host result out, through the public host-batch call
     # (torchimize_b200.pipeline.solve_host_batches): every step copies ITS inputs (p0, t, y) from pinned host memory and
     # reads its finals back; the copy of step k+1 runs on a copy stream while step k solves (two device slots).  The
@@ -328,6 +358,9 @@ def run_ours(args):
                         'api': 'torchimize_b200.pipeline.solve_host_batches (double-buffered H2D on a copy stream; K copies + '
                                'K solves + K result reads inside the timed region)'},
                 'gpu_launches': launches, 'roofline': roof, 'clocks': sampler.summary()}
+        also_lm['value'] = B * world * lm_steps / (ms_lm * 1e-3)
+        also_lm['frac_of_hbm_peak'] = also_lm['achieved_GBps'] / peak
+        line['also_lm'] = also_lm
         if world == 1 and not args.no_cpu_baseline:
             line['cpu_baseline'] = cpu_baseline(work)
         print(json.dumps(line), flush=True)

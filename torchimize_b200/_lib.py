@@ -8,7 +8,7 @@ import threading
 import torch
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, 'libnlls_b200.so')
+LIB_PATH = os.environ.get('NLLS_LIB') or os.path.join(_HERE, 'libnlls_b200.so')   # NLLS_LIB: A/B an older build
 CSRC = os.path.join(_HERE, 'csrc')
 
 F32, F64 = 0, 1

@@ -258,6 +258,7 @@ k_model_normal_eq_staged(const T* __restrict__ p, const T* __restrict__ x, const
   // ---- producer state (thread 0): next tile to issue = (problem pb, sample offset pn0) into stage pst
   long long pb = blockIdx.x;
   int pn0 = 0, pst = 0;
+  unsigned char psel = (sel && tid == 0 && pb < B) ? sel[pb] : (unsigned char)0;
   auto issue = [&]() {
     if (pb >= B) return;
     const int rows = min(TN, N - pn0);
@@ -268,11 +269,15 @@ k_model_normal_eq_staged(const T* __restrict__ p, const T* __restrict__ x, const
     const T* src = y + pb * ybs + pn0;
     for (int c = 0; c < Cy; ++c, src += ycs, dst += TN) bulk_g2s(dst, src, bytes, bar);
     if (has_prev) {
-      const T* ps = (sel ? (sel[pb] ? fB : fA) : f_prev) + pb * (long long)C * N + pn0;
+      const T* ps = (sel ? (psel ? fB : fA) : f_prev) + pb * (long long)C * N + pn0;
       for (int c = 0; c < C; ++c, ps += N, dst += TN) bulk_g2s(dst, ps, bytes, bar);
     }
     pn0 += TN;
-    if (pn0 >= N) { pn0 = 0; pb += gridDim.x; }
+    if (pn0 >= N) {
+      pn0 = 0;
+      pb += gridDim.x;
+      if (sel && pb < B) psel = sel[pb];                     // buffer role of the NEXT problem: in flight until its first tile
+    }
     pst = (pst + 1 == NSTAGE) ? 0 : pst + 1;
   };
   if (tid == 0) {
@@ -457,6 +462,7 @@ k_model_normal_eq_vec(const T* __restrict__ p, const T* __restrict__ x, const T*
 
   long long pb = blockIdx.x;
   int pn0 = 0, pst = 0;
+  unsigned char psel = (sel && tid == 0 && pb < B) ? sel[pb] : (unsigned char)0;
   auto issue = [&]() {
     if (pb >= B) return;
     const int rows = min(TN, N - pn0);
@@ -467,11 +473,15 @@ k_model_normal_eq_vec(const T* __restrict__ p, const T* __restrict__ x, const T*
     const T* src = y + pb * ybs + pn0;
     for (int c = 0; c < Cy; ++c, src += ycs, dst += TN) bulk_g2s(dst, src, bytes, bar);
     if (has_prev) {
-      const T* ps = (sel ? (sel[pb] ? fB : fA) : f_prev) + pb * (long long)C * N + pn0;
+      const T* ps = (sel ? (psel ? fB : fA) : f_prev) + pb * (long long)C * N + pn0;
       for (int c = 0; c < C; ++c, ps += N, dst += TN) bulk_g2s(dst, ps, bytes, bar);
     }
     pn0 += TN;
-    if (pn0 >= N) { pn0 = 0; pb += gridDim.x; }
+    if (pn0 >= N) {
+      pn0 = 0;
+      pb += gridDim.x;
+      if (sel && pb < B) psel = sel[pb];                     // buffer role of the NEXT problem: in flight until its first tile
+    }
     pst = (pst + 1 == NSTAGE) ? 0 : pst + 1;
   };
   if (tid == 0) {
@@ -654,6 +664,7 @@ k_model_wpp(const T* __restrict__ p, const T* __restrict__ x, const T* __restric
   long long fb = wid;                       // producer cursor: next chunk to request
   int fq = 0;
   unsigned fst = 0;
+  unsigned char fsel = (sel && lane == 0 && fb < B) ? sel[fb] : (unsigned char)0;
   auto issue = [&]() {
     if (fb >= B) return;
     if (lane == 0) {
@@ -664,12 +675,16 @@ k_model_wpp(const T* __restrict__ p, const T* __restrict__ x, const T* __restric
       const T* src = y + fb * ybs + n0;
       for (int c = 0; c < Cy; ++c, src += ycs, dst += CH) bulk_g2s(dst, src, bytes, &bars[fst]);
       if (has_prev) {
-        const T* ps = (sel ? (sel[fb] ? prevB : prevA) : f_prev) + fb * prev_bs + n0;
+        const T* ps = (sel ? (fsel ? prevB : prevA) : f_prev) + fb * prev_bs + n0;
         for (int c = 0; c < CP; ++c, ps += N, dst += CH) bulk_g2s(dst, ps, bytes, &bars[fst]);
       }
     }
     fst = (fst + 1 == NSTAGE) ? 0 : fst + 1;
-    if (++fq == QN) { fq = 0; fb += nwarps; }
+    if (++fq == QN) {
+      fq = 0;
+      fb += nwarps;
+      if (sel && lane == 0 && fb < B) fsel = sel[fb];        // next problem's buffer role, loaded a whole problem ahead of its use
+    }
   };
 #pragma unroll
   for (int s = 0; s < NSTAGE; ++s) issue();
