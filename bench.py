@@ -338,6 +338,9 @@ def run_ours(args):
             'traffic': traffic, 'peak_source': 'MEASURED_PEAKS.json hbm_gbs (measured)' if peaks else 'fallback 6650 GB/s',
             'avg_launch_ms': avg_ms, 'launches_timed': len(live), 'share_of_step': share, 'algorithmic_bytes_per_launch':
             bytes_per_problem * B, 'bytes_note': byte_note,
+            'achieved_y_only': (esz * C * N * B / (avg_ms * 1e-3) / 1e9) if top_name == 'nlls_model_normal_eq' else None,
+            'y_only_note': 'SURVEY 8d lower bound s*C*N (data read once, f_prev recomputed instead of stored): the kernel stores f '
+                           'because a second model evaluation per sample costs more than the 2*s*C*N bytes it saves (DESIGN.md 4)',
             'kernels_ms_per_step': {k: sum(v) / args.steps for k, v in per.items()},
             'timing': 'CUDA events around every launch inside the timed steps (sustained clocks)'}
 
