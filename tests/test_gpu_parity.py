@@ -461,3 +461,25 @@ def test_speculative_lm_schedule_is_bit_identical_to_two_pass(dn, meth):
     same = (outs[0] == outs[1]) | (torch.isnan(outs[0]) & torch.isnan(outs[1]))
     assert bool(same.all())
     assert bool((outs[0][1:] == outs[0][:-1]).all(dim=2).any()), 'no rejected step in the trajectory: test is vacuous'
+
+
+def test_fp64_exp_nonpos_accuracy():
+    """csrc/models.cuh::exp_nonpos (the fp64 exp of every built-in and compiled model) against torch.exp over its whole
+    range, through the C ABI: the compiled Gaussian + offset example with a = 1, c = 0, sigma = 1/sqrt(2), mu = 0 has
+    m(x) = exp(-x^2), and with y = 0 the Jacobian column of the offset is 2 (y - m) * (-1) = 2 m (an exact doubling)."""
+    from torchimize_b200.models import compile_model_file
+    import os
+    from conftest import ROOT
+    model = compile_model_file(os.path.join(ROOT, 'torchimize_b200', 'user_models', 'gauss_offset.cuh'))
+    x = torch.cat([torch.linspace(0, 26.5, 200001, dtype=torch.float64), torch.tensor([26.6, 27., 30., 1e3], dtype=torch.float64)])
+    p = torch.tensor([[1., 0., 0.5 ** .5, 0.]], dtype=torch.float64)
+    y = torch.zeros(1, x.numel(), dtype=torch.float64)
+    got = model.jac(p.to(DEV), x.to(DEV), y.to(DEV))[0, 0, :, 3].cpu() / 2
+    arg = -(x * x) * (0.5 / (p[0, 2] * p[0, 2]))                 # what load()/eval() form: -(d*d) * (0.5 / sigma^2)
+    want = torch.exp(arg)
+    big = want > 1e-300
+    rel = ((got[big] - want[big]).abs() / want[big]).max()
+    assert float(rel) <= 2.3e-16, f'exp_nonpos: {float(rel):.2e} relative'      # 1 ulp = 2.2e-16
+    assert float(got[~big].max()) <= 1e-300                       # flushed tail
+    assert bool(torch.isnan(model.cost(torch.tensor([[1., float('nan'), 1., 0.]], dtype=torch.float64, device=DEV),
+                                       x[:8].to(DEV), y[:, :8].to(DEV))).all())

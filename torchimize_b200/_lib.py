@@ -118,8 +118,15 @@ def build_plugin(source: str, name: str = 'user', verbose=False):
            os.path.join(CSRC, 'fused_models.cu'), os.path.join(CSRC, 'api.cu'), '-lcudart']
     r = subprocess.run(cmd, capture_output=True, text=True)
     if r.returncode != 0:
+        import shutil
+        shutil.rmtree(out_dir, ignore_errors=True)
         raise NllsError(f'compiling user model {name!r} failed:\n' + r.stdout[-3000:] + r.stderr[-6000:])
     os.replace(tmp, so)
+    # older builds of the same model (other kernel-source hashes) are dead weight in the tree: drop them
+    import shutil
+    for d in os.listdir(JIT_DIR):
+        if d.startswith(safe + '_') and d != os.path.basename(out_dir) and len(d) == len(safe) + 17:
+            shutil.rmtree(os.path.join(JIT_DIR, d), ignore_errors=True)
     if verbose:
         print('built', so)
     return so

@@ -31,10 +31,35 @@ __device__ __forceinline__ float ex2_approx(float x) {
 // exp(-a c) for a >= 0 with a per-problem constant c prepared once: fp32 folds the sign and log2(e) into the constant
 // (ONE FMUL + MUFU.EX2 per evaluation, no negation instruction); fp64 keeps CUDA's exp on the exactly negated product.
 template <typename T> struct ExpNeg;
+// fp64 exp for NON-POSITIVE arguments (every call site below evaluates exp(-a), a >= 0).  CUDA's exp() costs ~30
+// instructions plus ~20 moves that materialise its polynomial constants as immediates (IMAD.MOV was 18 % of the warp
+// instructions of the fp64 fused kernel, profiles/r01h_fused_ncu.txt); here the coefficients sit in constant memory, so
+// every DFMA reads its coefficient as a c[bank][offset] operand.  Cody-Waite reduction x = n ln2 + r, |r| <= ln2/2,
+// degree-13 Taylor polynomial (remainder < 5e-18 relative), scaling by 2^n through the exponent field; < 1 ulp measured
+// against torch.exp (tests/test_gpu_parity.py::test_fp64_exp_nonpos_accuracy).  Results below 2^-1020 (x < -707) are
+// flushed to 0: the reference's denormal tail (< 1e-307) is absolutely negligible in every sum it enters.  NaN propagates.
+__constant__ double kExpTaylor[12] = {1.6059043836821613e-10, 2.08767569878681e-09, 2.505210838544172e-08, 2.755731922398589e-07,
+                                      2.7557319223985893e-06, 2.48015873015873e-05, 0.0001984126984126984, 0.001388888888888889,
+                                      0.008333333333333333, 0.041666666666666664, 0.16666666666666666, 0.5};
+__device__ __forceinline__ double exp_nonpos(double x) {
+  if (x < -707.0) return 0.0;
+  const double magic = 6755399441055744.0;                   // 1.5 * 2^52: fma rounds x*log2(e) to the nearest integer
+  double t = fma(x, 1.4426950408889634, magic);
+  const int n = __double2loint(t);
+  t -= magic;
+  double r = fma(t, -0.6931471803691238, x);                 // ln2 split: high part has 21 trailing zero bits (t*hi exact)
+  r = fma(t, -1.9082149292705877e-10, r);
+  double q = kExpTaylor[0];
+#pragma unroll
+  for (int i = 1; i < 12; ++i) q = fma(q, r, kExpTaylor[i]);
+  q = fma(q, r, 1.0);
+  q = fma(q, r, 1.0);
+  return __hiloint2double(__double2hiint(q) + (n << 20), __double2loint(q));
+}
 template <> struct ExpNeg<double> {
   static __device__ __forceinline__ double prep(double c) { return c; }
-  static __device__ __forceinline__ double eval(double a, double c) { return exp(-a * c); }
-  static __device__ __forceinline__ double sq(double x) { return exp(-(x * x)); }
+  static __device__ __forceinline__ double eval(double a, double c) { return exp_nonpos(-a * c); }
+  static __device__ __forceinline__ double sq(double x) { return exp_nonpos(-(x * x)); }
 };
 template <> struct ExpNeg<float> {
   static __device__ __forceinline__ float prep(float c) { return c * -1.4426950408889634f; }
@@ -54,7 +79,13 @@ template <> __device__ __forceinline__ float t_erf<float>(float x) { return erff
 //         ~16 instructions and no divergent branch instead of erff's two-sided ~40, and E is needed for
 //         the derivative anyway.  Fit: least squares with Lawson reweighting on the relative error.
 template <typename T> __device__ __forceinline__ T one_plus_erf(T x, T E);
-template <> __device__ __forceinline__ double one_plus_erf<double>(double x, double) { return 1.0 + erf(x); }
+template <> __device__ __forceinline__ double one_plus_erf<double>(double x, double) {
+  // |x| >= 6: 1 - erf(|x|) < 2.2e-17 < 2^-54, so erf rounds to +-1 exactly and 1 + erf(x) is exactly 2 or 0 — the value
+  // the reference's torch.erf produces.  Samples are adjacent along the abscissa, so whole warps take this exit in the
+  // tails of a peak (86 % of the samples of the EMG workloads) and skip CUDA's erf (~90 instructions, one division).
+  if (fabs(x) >= 6.0) return x > 0.0 ? 2.0 : 0.0;
+  return 1.0 + erf(x);
+}
 template <> __device__ __forceinline__ float one_plus_erf<float>(float x, float E) {
   const float ax = fabsf(x);
   float t;                                         // MUFU.RCP alone (1 ulp): __frcp_rn adds a Newton step and a slow-path branch
