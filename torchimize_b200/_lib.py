@@ -116,7 +116,10 @@ def build_plugin(source: str, name: str = 'user', verbose=False):
     cmd = ['nvcc', '-O3', '-std=c++17', '-gencode', 'arch=compute_100a,code=sm_100a', '-lineinfo', '-Xcompiler', '-fPIC',
            f'-DNLLS_USER_MODEL_HEADER="{hdr}"', '-I', CSRC, '-shared', '-o', tmp,
            os.path.join(CSRC, 'fused_models.cu'), os.path.join(CSRC, 'api.cu'), '-lcudart']
-    r = subprocess.run(cmd, capture_output=True, text=True)
+    try:
+        r = subprocess.run(cmd, capture_output=True, text=True)
+    except FileNotFoundError as e:
+        raise NllsError('compile_model needs nvcc on PATH (CUDA 12.8+ with sm_100a support): ' + str(e)) from e
     if r.returncode != 0:
         import shutil
         shutil.rmtree(out_dir, ignore_errors=True)
