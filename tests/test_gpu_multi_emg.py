@@ -48,24 +48,66 @@ def test_multi_emg_solves_match_the_oracle_fp64(solver, K):
     model = MultiEMGModel(K)
     ours = lsq_lma_parallel if solver == 'lma' else lsq_gna_parallel
     ref = getattr(O, solver)(p0.clone(), M.multi_emg_cost, M.multi_emg_jac, args=(t, y), **kw)
-    p = p0.clone().to(DEV)
-    got = ours(p, model.cost, model.jac, args=(t.to(DEV), y.to(DEV)), **kw)
-    compare_plist(got, torch.stack(ref.p_list), 'f64', f'{K}-peak EMG {solver}')
-    assert float(((p.cpu() - gt).abs() / gt.abs().clamp(min=1.)).max()) < 5e-2
+    for fused in (True, False):                                   # tensor-core fused kernel / materialised J + K1
+        p = p0.clone().to(DEV)
+        got = ours(p, model.cost, model.jac, args=(t.to(DEV), y.to(DEV)), fused=fused, **kw)
+        compare_plist(got, torch.stack(ref.p_list), 'f64', f'{K}-peak EMG {solver} fused={fused}')
+        assert float(((p.cpu() - gt).abs() / gt.abs().clamp(min=1.)).max()) < 5e-2
 
 
 @pytest.mark.gpu
-def test_multi_emg_has_no_fused_kernels_and_says_so():
+@pytest.mark.parametrize('dn', ['f64', 'f32'])
+@pytest.mark.parametrize('C', [1, 3])
+@pytest.mark.parametrize('K', [2, 3, 4])
+def test_multi_emg_tensor_core_fused_normal_equations_match_the_oracle(K, C, dn):
+    """nlls_model_normal_eq for P = 8|12|16 (k_model_normal_eq_mma: DMMA over the per-warp tile of k rows) against the
+    oracle's newton step on the materialised J, two consecutive iterations (the second reads f_prev), ragged N."""
+    from oracle import nlls_oracle as O, models as M
+    from torchimize_b200 import _lib
+    dt = torch.float64 if dn == 'f64' else torch.float32
+    tol = 1e-11 if dn == 'f64' else 3e-4
+    B, N, P = 7, 1000 + 13, 4 * K
+    p0, t, y, _ = multi_emg_batch(B, K, N, 9, dt, C=C)
+    w = torch.linspace(1., 1.4, C, dtype=dt)
+    pd, td, yd, wd = (v.to(DEV) for v in (p0, t, y, w))
+    fpp = torch.zeros(2, B, C, N, dtype=dt, device=DEV)
+    g = torch.empty(B, P, dtype=dt, device=DEV)
+    H = torch.empty(B, P, P, dtype=dt, device=DEV)
+    st = torch.empty(B, 4, dtype=torch.float64, device=DEV)
+    ctrl = _lib.new_ctrl(DEV)
+    f_prev = None
+    for it, scale in enumerate((1., 1.01)):
+        ctrl.view(torch.int32)[1] = it                            # ctrl->iters selects the ping-pong roles
+        pi = (p0 * scale).to(DEV)
+        _lib.call('nlls_model_normal_eq', _lib.MODEL_MULTI_EMG, _lib.dtype_code(pi), _lib.ptr(pi), P, _lib.ptr(td), _lib.ptr(yd),
+                  C * N, N, _lib.ptr(wd), C, B, C, N, _lib.ptr(fpp[0]), _lib.ptr(fpp[1]), _lib.ptr(g), _lib.ptr(H), _lib.ptr(st),
+                  _lib.ptr(ctrl), _lib.stream_ptr())
+        f = M.multi_emg_cost(p0 * scale, t, y)
+        J = M.multi_emg_jac(p0 * scale, t, y)
+        g0, H0 = O.normal_equations(f, J, w)
+        assert float((g.cpu() - g0).abs().max()) <= tol * float(g0.abs().max())
+        assert float((H.cpu() - H0).abs().max()) <= tol * float(H0.abs().max())
+        assert float((fpp[it & 1].cpu() - f).abs().max()) <= tol * float(f.abs().max())
+        assert torch.allclose(st[:, 0].cpu(), O.cost_sum_stat(f).double(), rtol=1e-9 if dn == 'f64' else 1e-3)
+        assert torch.allclose(st[:, 2].cpu(), (f.double() ** 2).sum((1, 2)), rtol=1e-9 if dn == 'f64' else 1e-3)
+        if f_prev is not None:
+            assert torch.allclose(st[:, 1].cpu(), ((f_prev - f).double() ** 2).sum((1, 2)), rtol=1e-9 if dn == 'f64' else 1e-2)
+        f_prev = f
+
+
+@pytest.mark.gpu
+def test_multi_emg_gd_takes_the_tensor_path_and_the_abi_says_what_exists():
     from torchimize_b200 import _lib
     from torchimize_b200.models import MultiEMGModel, fused_model_of
     model = MultiEMGModel(4)
-    assert fused_model_of(model.cost, model.jac) is None          # solvers take the tensor path
+    assert fused_model_of(model.cost, model.jac, 'gn') is model and fused_model_of(model.cost, model.jac, 'lm') is model
+    assert fused_model_of(model.cost, model.jac, 'gd') is None    # gradient_descent_parallel: nlls_model_eval + K1
     p0, t, y, _ = multi_emg_batch(2, 4, 64, 1, torch.float64)
     g = torch.empty(2, 16, dtype=torch.float64, device=DEV)
     H = torch.empty(2, 16, 16, dtype=torch.float64, device=DEV)
     st = torch.empty(2, 4, dtype=torch.float64, device=DEV)
     w = torch.ones(1, dtype=torch.float64, device=DEV)
     pd, td, yd = p0.to(DEV), t.to(DEV), y.to(DEV)
-    with pytest.raises(_lib.NllsError, match='no fused'):
-        _lib.call('nlls_model_normal_eq', _lib.MODEL_MULTI_EMG, _lib.F64, _lib.ptr(pd), 16, _lib.ptr(td), _lib.ptr(yd), 64, 0,
+    with pytest.raises(_lib.NllsError, match='only nlls_model_eval'):
+        _lib.call('nlls_model_normal_eq_gda', _lib.MODEL_MULTI_EMG, _lib.F64, _lib.ptr(pd), 16, _lib.ptr(td), _lib.ptr(yd), 64, 0,
                   _lib.ptr(w), 1, 2, 1, 64, None, None, _lib.ptr(g), _lib.ptr(H), _lib.ptr(st), None, _lib.stream_ptr())

@@ -1293,6 +1293,157 @@ k_model_eval(const T* __restrict__ p, const T* __restrict__ x, const T* __restri
   }
 }
 
+// ------------------------------------------------------------------ fused normal equations, 8 < P <= 16, fp64 tensor cores
+// Multi-peak models (cfg-4: four EMG peaks, P = 16) have too many accumulators for the register-resident kernels above
+// (g and the packed triangle of H would be 152 fp64 values per thread).  Here a warp owns batches of 32 consecutive
+// samples: lane L evaluates sample L once (model value m and k = -dm/dp, all peaks), loops the costs for the residuals
+// (f written, f_prev read, statistics, s2 = 4 sum_c w_c r_c^2, s3 = 2 sum_c w_c r_c^3 as in k_model_normal_eq) and drops
+// its k row into a per-warp shared tile [32][16] (row stride 160 B: conflict-free 128-bit reads).  The 32 x 16 tile is
+// then reduced on the fp64 tensor cores exactly like K1's k_normal_eq_dmma_vec (mma.sync.m8n8k4.f64 -> DMMA): lane
+// (gi, k) reads the two columns {2 gi, 2 gi + 1} of row 4u + k; H += (s2 k) k^T takes 3 DMMAs per 4 rows, g += s3 k
+// two DFMAs.  J [B,C,N,P] (17 GB at cfg-4) is never written or read: per problem-iteration the kernel moves 3 s C N
+// bytes instead of the tensor path's s C N (2 P + 4).
+__device__ __forceinline__ void dmma_884_acc(double& d0, double& d1, double a, double b) {
+  asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
+               : "+d"(d0), "+d"(d1) : "d"(a), "d"(b));
+}
+
+template <typename T, typename Model, int NW, int MINB>
+__global__ void __launch_bounds__(NW * 32, MINB)
+k_model_normal_eq_mma(const T* __restrict__ p, const T* __restrict__ x, const T* __restrict__ y, long long ybs, long long ycs,
+                      const T* __restrict__ w, int wlen, long long B, int C, int N, T* fA, T* fB, T* __restrict__ gout,
+                      T* __restrict__ Hout, double* __restrict__ stats, const nlls_ctrl* ctrl,
+                      const unsigned char* __restrict__ sel) {
+  if (is_done(ctrl)) return;
+  constexpr int P = Model::P, NB = 2, PP = 16, RW = PP * PP + PP + 2, TPB = NW * 32, ROWD = 20;
+  static_assert(P <= PP && P % NB == 0, "tensor-core fused kernel: even P <= 16");
+  extern __shared__ double smem_d[];
+  double* red = smem_d;                          // [NW][RW]: H (canonical entries), g, {sd, sq}
+  double* tiles = red + NW * RW;                 // [NW][32][ROWD]
+  double* csum = tiles + NW * 32 * ROWD;         // [C][TPB] per-thread per-cost sums of f
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int k = lane & 3, gi = lane >> 2;
+  double* tile = tiles + warp * 32 * ROWD;
+  const int it = iter_index(ctrl);
+  const int NBATCH = (N + 31) >> 5;
+
+  for (long long b = blockIdx.x; b < B; b += gridDim.x) {
+    T* f_out = (it & 1) ? fB : fA;
+    const T* f_prev = (it > 0 && fA) ? ((it & 1) ? fA : fB) : nullptr;
+    if (sel) { const bool s1 = sel[b] != 0; f_out = s1 ? fA : fB; f_prev = s1 ? fB : fA; }
+    if (f_out) f_out += b * (long long)C * N;
+    if (f_prev) f_prev += b * (long long)C * N;
+    Model M;
+    M.load(p + b * P);
+    double Ht[3][2], Gt[NB];
+#pragma unroll
+    for (int i = 0; i < 3; ++i) Ht[i][0] = Ht[i][1] = 0.0;
+    Gt[0] = Gt[1] = 0.0;
+    double sd = 0.0, sq = 0.0;
+    for (int c = 0; c < C; ++c) csum[c * TPB + tid] = 0.0;
+    for (int bt = warp; bt < NBATCH; bt += NW) {
+      const int n = (bt << 5) + lane;
+      const bool live = n < N;
+      T m = T(0), kk[P];
+#pragma unroll
+      for (int i = 0; i < P; ++i) kk[i] = T(0);
+      T s2 = T(0), s3 = T(0);
+      if (live) {
+        M.eval(ld_cached(x + n), m, kk);
+        const T* yb = y + b * ybs + n;
+        for (int c = 0; c < C; ++c) {
+          const T wc = w[wlen == 1 ? 0 : c];
+          const T r = ld_cached(yb + c * ycs) - m;
+          const T fv = mul_rn(r, r);
+          if (f_out) stg_stream(f_out + (long long)c * N + n, fv);
+          if (f_prev) { const T d = ldg_stream(f_prev + (long long)c * N + n) - fv; sd = fma((double)d, (double)d, sd); }
+          sq = fma((double)fv, (double)fv, sq);
+          csum[c * TPB + tid] += (double)fv;
+          const T wf = wc * fv;
+          s2 += wf;
+          s3 = fma(wf, r, s3);
+        }
+      }
+      const double s2d = (double)(T(4) * s2), s3d = (double)(T(2) * s3);
+#pragma unroll
+      for (int i = 0; i < PP; i += 2) {
+        double2 v;
+        v.x = i < P ? (double)kk[i < P ? i : 0] : 0.0;
+        v.y = i + 1 < P ? (double)kk[i + 1 < P ? i + 1 : 0] : 0.0;
+        *reinterpret_cast<double2*>(tile + lane * ROWD + i) = v;
+      }
+      __syncwarp();
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        const int row = 4 * u + k;
+        const double2 v = *reinterpret_cast<const double2*>(tile + row * ROWD + NB * gi);
+        const double s2k = __shfl_sync(0xffffffffu, s2d, row), s3k = __shfl_sync(0xffffffffu, s3d, row);
+        const double a0 = v.x * s2k, a1 = v.y * s2k;
+        dmma_884_acc(Ht[0][0], Ht[0][1], a0, v.x);      // block (0,0)
+        dmma_884_acc(Ht[1][0], Ht[1][1], a0, v.y);      // block (0,1)
+        dmma_884_acc(Ht[2][0], Ht[2][1], a1, v.y);      // block (1,1)
+        Gt[0] = fma(v.x, s3k, Gt[0]);
+        Gt[1] = fma(v.y, s3k, Gt[1]);
+      }
+      __syncwarp();                                // the tile is rewritten by the next batch
+    }
+    // ---- warp partials -> shared memory; entry (i, j) of block (I, Jb) is H[NB*gi + I][NB*gj + Jb]  (as in K1)
+#pragma unroll
+    for (int I = 0; I < NB; ++I) { Gt[I] += shfl_xor(Gt[I], 1); Gt[I] += shfl_xor(Gt[I], 2); }
+    sd = warp_sum(sd);
+    sq = warp_sum(sq);
+    double* r = red + warp * RW;
+    {
+      int idx = 0;
+#pragma unroll
+      for (int I = 0; I < NB; ++I)
+#pragma unroll
+        for (int Jb = I; Jb < NB; ++Jb, ++idx) {
+          r[(NB * gi + I) * PP + NB * (2 * k) + Jb] = Ht[idx][0];
+          r[(NB * gi + I) * PP + NB * (2 * k + 1) + Jb] = Ht[idx][1];
+        }
+    }
+    if (k == 0) {
+#pragma unroll
+      for (int I = 0; I < NB; ++I) r[PP * PP + NB * gi + I] = Gt[I];
+    }
+    if (lane == 0) { r[PP * PP + PP] = sd; r[PP * PP + PP + 1] = sq; }
+    __syncthreads();
+    for (int e = tid; e < P * P; e += TPB) {
+      const int i = e / P, j = e - i * P;
+      const int lo = min(i, j), hi = max(i, j);
+      const int off = ((lo % NB) <= (hi % NB)) ? lo * PP + hi : hi * PP + lo;
+      double sacc = 0.0;
+#pragma unroll
+      for (int ww = 0; ww < NW; ++ww) sacc += red[ww * RW + off];
+      Hout[b * P * P + e] = (T)sacc;
+    }
+    if (tid < P) {
+      double sacc = 0.0;
+#pragma unroll
+      for (int ww = 0; ww < NW; ++ww) sacc += red[ww * RW + PP * PP + tid];
+      gout[b * P + tid] = (T)sacc;
+    }
+    if (warp == NW - 1) {
+      double tot = 0.0;
+      for (int c = 0; c < C; ++c) {
+        double sacc = 0.0;
+#pragma unroll
+        for (int ww = 0; ww < NW; ++ww) sacc += csum[c * TPB + ww * 32 + lane];
+        sacc = warp_sum(sacc);
+        tot = fma(sacc, sacc, tot);
+      }
+      if (lane == 0) {
+        double s1 = 0.0, s2t = 0.0;
+#pragma unroll
+        for (int ww = 0; ww < NW; ++ww) { s1 += red[ww * RW + PP * PP + PP]; s2t += red[ww * RW + PP * PP + PP + 1]; }
+        stats[b * 4 + 0] = tot; stats[b * 4 + 1] = s1; stats[b * 4 + 2] = s2t; stats[b * 4 + 3] = 0.0;
+      }
+    }
+    __syncthreads();
+  }
+}
+
 // ------------------------------------------------------------------------------ dispatch
 template <typename K>
 static int grid_for(K kernel, int tpb, size_t smem, long long B) {
@@ -1588,11 +1739,34 @@ static int run_op(Op op, const ModelArgs& a) {
   return NLLS_E_MODEL;
 }
 
-// models that only exist on the materialising path (P > 6: the fused kernels keep g and H in registers)
+// models with 6 < P <= 16: materialising kernel + the tensor-core fused normal equations (GN and speculative LM);
+// no fused GD / two-pass trial-cost kernels (gradient_descent_parallel takes the tensor path for them)
 template <typename T, typename Model>
-static int run_eval_only(Op op, const ModelArgs& a, const char* name) {
+static int run_wide(Op op, const ModelArgs& a, const char* name) {
   if (op == OP_EVAL) return launch_eval<T, Model>(a);
-  set_error("%s (P=%d) has no fused normal-equation kernels: use the tensor path (nlls_model_eval + nlls_normal_eq)", name, Model::P);
+  if (op == OP_NEQ) {
+    constexpr int RW = 16 * 16 + 16 + 2;
+    auto go = [&](auto kern, int NWv) {
+      const int TPB = NWv * 32;
+      const size_t smem = ((size_t)NWv * RW + (size_t)NWv * 32 * 20 + (size_t)a.C * TPB) * 8;
+      if (smem > 200 * 1024) { set_error("fused model path: too many costs (C=%d)", a.C); return (int)NLLS_E_SHAPE; }
+      const int grid = grid_for(kern, TPB, smem, a.B);
+      kern<<<grid, TPB, smem, a.st>>>((const T*)a.p, (const T*)a.x, (const T*)a.y, a.ybs, a.ycs, (const T*)a.w, a.wlen, a.B,
+                                      a.C, a.N, (T*)a.fA, (T*)a.fB, (T*)a.g, (T*)a.H, a.stats, a.ctrl, a.sel);
+      return check_launch("nlls_model_normal_eq(mma)");
+    };
+    switch (fused_variant()) {                               // tuning hook (occupancy against registers)
+#ifndef NLLS_USER_MODEL_HEADER
+      case 1: return go(k_model_normal_eq_mma<T, Model, 4, 5>, 4);   // 96 registers, 20 warps/SM: 6.08 ms at cfg-4
+      case 2: return go(k_model_normal_eq_mma<T, Model, 4, 4>, 4);   // 128 registers, 16 warps/SM: 6.14 ms
+      case 3: return go(k_model_normal_eq_mma<T, Model, 4, 3>, 4);   // 163 registers, 12 warps/SM: 6.48 ms (198 regs, 4 warps: 8.4 ms)
+#endif
+      // the kernel is bound by the latency of the fp64 model math: occupancy beats registers (profiles/r01j): 80 registers
+      // (a few spills), 24 warps/SM: 5.93 ms
+      default: return go(k_model_normal_eq_mma<T, Model, 4, 6>, 4);
+    }
+  }
+  set_error("%s (P=%d): only nlls_model_eval, nlls_model_normal_eq and nlls_model_lm_trial exist for P > 6", name, Model::P);
   return NLLS_E_MODEL;
 }
 
@@ -1607,9 +1781,9 @@ static int run_model(int model, int P, Op op, const ModelArgs& a) {
   if (model == NLLS_MODEL_EMG && P == 4) return run_op<T, EmgModel<T>>(op, a);
   if (model == NLLS_MODEL_SKEWGAUSS && P == 4) return run_op<T, SkewGaussModel<T, 4>>(op, a);
   if (model == NLLS_MODEL_SKEWGAUSS && P == 5) return run_op<T, SkewGaussModel<T, 5>>(op, a);
-  if (model == NLLS_MODEL_MULTI_EMG && P == 8) return run_eval_only<T, MultiEmgModel<T, 2>>(op, a, "2-peak EMG");
-  if (model == NLLS_MODEL_MULTI_EMG && P == 12) return run_eval_only<T, MultiEmgModel<T, 3>>(op, a, "3-peak EMG");
-  if (model == NLLS_MODEL_MULTI_EMG && P == 16) return run_eval_only<T, MultiEmgModel<T, 4>>(op, a, "4-peak EMG");
+  if (model == NLLS_MODEL_MULTI_EMG && P == 8) return run_wide<T, MultiEmgModel<T, 2>>(op, a, "2-peak EMG");
+  if (model == NLLS_MODEL_MULTI_EMG && P == 12) return run_wide<T, MultiEmgModel<T, 3>>(op, a, "3-peak EMG");
+  if (model == NLLS_MODEL_MULTI_EMG && P == 16) return run_wide<T, MultiEmgModel<T, 4>>(op, a, "4-peak EMG");
   set_error("unknown model %d with P=%d (EMG: P=4, skewed Gaussian: P=4|5, multi-peak EMG: P=8|12|16)", model, P);
   return NLLS_E_MODEL;
 #endif

@@ -172,7 +172,9 @@ def solve(solver, p, function, jac_function, args, wvec, ftol, ptol, gtol, max_i
         reduce_hook = _default_reduce_hook
     work_p = p if p.is_contiguous() else p.contiguous()
     ws = Workspace(work_p, wvec, solver)
-    model = fused_model_of(function, jac_function) if fused else None
+    # 'lm' = speculative schedule (nlls_model_lm_trial), 'lm2' = two-pass schedule (needs nlls_model_cost_stat)
+    skey = {GN: 'gn', LM: 'lm' if SPECULATIVE_LM else 'lm2', GD: 'gd'}[solver]
+    model = fused_model_of(function, jac_function, skey) if fused else None
     st = _lib.stream_ptr
     B, P, code = ws.B, ws.P, ws.code
     ctrl = _lib.ptr(ws.ctrl)

@@ -24,7 +24,7 @@ class FusedModel:
     model_id = -1
     n_params = ()
     lib = None            # plugin library of a compiled user model; None = libnlls_b200.so
-    fused_ops = True      # False: only the materialising kernel exists (solvers take the tensor path)
+    fused_solvers = ('gn', 'lm', 'lm2', 'gd')   # solvers with fused kernels for this model; the others take the tensor path
 
     def __init__(self, n_costs=None):
         # n_costs: number of cost channels when y is [B,N] (one data row shared by all costs, as in
@@ -87,10 +87,12 @@ class SkewGaussModel(FusedModel):
 
 class MultiEMGModel(FusedModel):
     """Sum of ``n_peaks`` (2..4) EMG peaks, p = [alpha_1, mu_1, sigma_1, eta_1, ...] (P = 4 n_peaks; SURVEY.md §8d, the
-    large-P workload of cfg-4).  Residuals and Jacobian are materialised by ``nlls_model_eval``; the solvers then run
-    the tensor path, whose normal equations go to the fp64 tensor cores for P > 8."""
+    large-P workload of cfg-4).  Gauss-Newton and Levenberg-Marquardt run the tensor-core fused kernel
+    (k_model_normal_eq_mma: the model is evaluated once per sample and the per-warp 32 x 16 tile of k rows is reduced
+    with fp64 DMMA; J is never materialised); gradient_descent_parallel, the two-pass LM schedule and ``fused=False``
+    take the tensor path (``nlls_model_eval`` + K1, also on the fp64 tensor cores for P > 8)."""
     model_id = _lib.MODEL_MULTI_EMG
-    fused_ops = False
+    fused_solvers = ('gn', 'lm')
 
     def __init__(self, n_peaks=4, n_costs=None):
         super().__init__(n_costs)
@@ -144,10 +146,12 @@ def model_owner_of(function, jac_function):
     return None
 
 
-def fused_model_of(function, jac_function):
-    """The FusedModel both callables belong to, else None (=> tensor path)."""
+def fused_model_of(function, jac_function, solver=None):
+    """The FusedModel both callables belong to (and that has fused kernels for `solver`), else None (=> tensor path)."""
     owner = getattr(function, '__self__', None)
-    if not isinstance(owner, FusedModel) or getattr(function, '__func__', None) is not FusedModel.cost or not owner.fused_ops:
+    if not isinstance(owner, FusedModel) or getattr(function, '__func__', None) is not FusedModel.cost:
+        return None
+    if solver is not None and solver not in owner.fused_solvers:
         return None
     if jac_function is None:
         return owner          # analytic Jacobian of the built-in model stands in for autograd's
