@@ -87,6 +87,25 @@ def test_compiled_emg_clone_is_bit_identical_to_the_builtin_kernels(dn):
 
 
 @pytest.mark.gpu
+def test_compiled_wide_model_runs_the_tensor_core_fused_kernel_like_the_builtin():
+    """A compiled functor with P = 8 (two EMG peaks) takes k_model_normal_eq_mma in the plugin: bit-identical to MultiEMGModel(2)."""
+    from torchimize_b200.functions import lsq_lma_parallel, lsq_gna_parallel, gradient_descent_parallel
+    from torchimize_b200.models import MultiEMGModel, compile_model
+    from test_gpu_multi_emg import multi_emg_batch
+    clone = compile_model('namespace nlls { template <typename T> struct UserModel : MultiEmgModel<T, 2> {}; }\n', 'emg2_clone')
+    assert clone.n_params == (8,) and clone.fused_solvers == ('gn', 'lm')
+    builtin = MultiEMGModel(2)
+    p0, t, y, _ = multi_emg_batch(16, 2, 1024, 4, torch.float64, C=2)
+    w = torch.ones(2, dtype=torch.float64, device=DEV)
+    for solver, kw in ((lsq_lma_parallel, dict(meth='lev')), (lsq_gna_parallel, {}), (gradient_descent_parallel, {})):
+        outs = []
+        for m in (clone, builtin):
+            p = p0.clone().to(DEV)
+            outs.append(torch.stack(solver(p, m.cost, m.jac, args=(t.to(DEV), y.to(DEV)), wvec=w, max_iter=20, **kw)))
+        assert outs[0].shape == outs[1].shape and bool((outs[0] == outs[1]).all())
+
+
+@pytest.mark.gpu
 def test_compiled_model_rejects_a_wrong_parameter_count():
     from torchimize_b200.functions import lsq_gna_parallel
     from torchimize_b200.models import compile_model_file

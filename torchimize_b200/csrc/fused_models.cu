@@ -1316,7 +1316,7 @@ k_model_normal_eq_mma(const T* __restrict__ p, const T* __restrict__ x, const T*
                       const unsigned char* __restrict__ sel) {
   if (is_done(ctrl)) return;
   constexpr int P = Model::P, NB = 2, PP = 16, RW = PP * PP + PP + 2, TPB = NW * 32, ROWD = 20;
-  static_assert(P <= PP && P % NB == 0, "tensor-core fused kernel: even P <= 16");
+  static_assert(P <= PP, "tensor-core fused kernel: P <= 16 (tile columns past P are zero)");
   extern __shared__ double smem_d[];
   double* red = smem_d;                          // [NW][RW]: H (canonical entries), g, {sd, sq}
   double* tiles = red + NW * RW;                 // [NW][32][ROWD]
@@ -1773,7 +1773,10 @@ static int run_wide(Op op, const ModelArgs& a, const char* name) {
 template <typename T>
 static int run_model(int model, int P, Op op, const ModelArgs& a) {
 #ifdef NLLS_USER_MODEL_HEADER
-  if (model == NLLS_MODEL_USER && P == UserModel<T>::P) return run_op<T, UserModel<T>>(op, a);
+  if (model == NLLS_MODEL_USER && P == UserModel<T>::P) {
+    if constexpr (UserModel<T>::P <= 6) return run_op<T, UserModel<T>>(op, a);        // register-resident fused kernels
+    else return run_wide<T, UserModel<T>>(op, a, "compiled model");                   // 6 < P <= 16: tensor-core fused kernel
+  }
   set_error("plugin library: model id %d / P=%d does not match the compiled functor (id %d, P=%d)", model, P, NLLS_MODEL_USER,
             UserModel<T>::P);
   return NLLS_E_MODEL;

@@ -108,6 +108,8 @@ class CompiledModel(FusedModel):
     def __init__(self, lib, n_params, name, n_costs=None):
         super().__init__(n_costs)
         self.lib, self.n_params, self.name = lib, (int(n_params),), name
+        if int(n_params) > 6:                  # tensor-core fused kernel: GN and speculative LM only (like MultiEMGModel)
+            self.fused_solvers = ('gn', 'lm')
 
     def __repr__(self):
         return f'CompiledModel({self.name!r}, P={self.n_params[0]})'
@@ -117,7 +119,7 @@ def compile_model(source, name='user', n_costs=None):
     """Compile a model written as a CUDA device functor and return it as a fused model object.
 
     ``source`` is CUDA C++ defining ``template <typename T> struct UserModel`` in namespace ``nlls`` with
-    ``static constexpr int P`` (<= 6 parameters), ``load(const T* p)``, ``T value(T x) const`` and
+    ``static constexpr int P`` (<= 16 parameters; above 6 the fp64 tensor-core fused kernel runs GN / LM and GD takes the tensor path), ``load(const T* p)``, ``T value(T x) const`` and
     ``void eval(T x, T& m, T (&k)[P]) const`` with ``k = -dm/dp`` (see torchimize_b200/user_models/gauss_offset.cuh;
     every helper of csrc/models.cuh is in scope).  The cost is the squared error used as residual, as for the
     built-in models.  nvcc compiles csrc/fused_models.cu for that functor (sm_100a only, ~1 min once, cached in
