@@ -148,3 +148,39 @@ def test_cfg4_full_size_k1_k2_properties():
     res = torch.einsum('bij,bj->bi', Hu, h) + g1
     assert float((res.norm(dim=1) / g1.norm(dim=1)).max()) <= 1e-12
     assert torch.equal(pt, p + h) and int(ctrl.view(torch.int32)[2]) == 0
+
+
+def test_cfg4_full_size_end_to_end_fused_tensor_core_path():
+    """BASELINE.json configs[3] end to end: lsq_lma_parallel / lsq_gna_parallel on B=32768 four-peak EMG fits
+    (C=1, N=4096, P=16, fp64) through the tensor-core fused kernel (k_model_normal_eq_mma + warp Cholesky K2):
+    fit quality against the ground truth, the slice property, and agreement with the materialised-J path (K1 DMMA)."""
+    import os
+    import sys
+    sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), 'scripts'))
+    from bench_configs import multi_emg_batch
+    from torchimize_b200.functions import lsq_lma_parallel
+    from torchimize_b200.models import MultiEMGModel
+    B, K, N = 32768, 4, 4096
+    p0, t, y, gt = multi_emg_batch(B, K, N, torch.float64)
+    model = MultiEMGModel(K)
+
+    def run(solver, ps, ys, fused=True, **kw):
+        p = ps.clone()
+        return torch.stack(solver(p, model.cost, model.jac, args=(t, ys), fused=fused, **kw))
+
+    gn = run(lsq_gna_parallel, p0, y, ftol=1e-8, ptol=1e-8, gtol=1e-8, max_iter=40)
+    lm = run(lsq_lma_parallel, p0, y, ftol=1e-8, ptol=1e-8, gtol=1e-8, max_iter=40, meth='lev')
+    scale = gt.abs().clamp(min=1.)
+    for name, out in (('gn', gn), ('lm', lm)):
+        assert 5 < out.shape[0] < 40, f'{name}: {out.shape[0]} iterations'
+        assert float(((out[-1] - gt).abs() / scale).max()) < 5e-2, name
+        assert float(model.cost(out[-1].contiguous(), t, y).sum((1, 2)).max()) < 4.0   # ~ N * noise^2 * kurtosis-ish, well below 1e-2 per sample
+    assert rel_err(gn[-1], lm[-1]) <= 1e-3                        # both stop near the same least-squares optimum (stop tests at 1e-8 on different trajectories)
+    # a slice iterated alone for the same number of steps (tolerances 0) gives the same bits
+    Kg = gn.shape[0]
+    sl = slice(777, 777 + 2048)
+    alone = run(lsq_gna_parallel, p0[sl], y[sl], ftol=0., ptol=0., gtol=0., max_iter=Kg)
+    assert alone.shape[0] == Kg and torch.equal(alone, gn[:, sl])
+    # the materialised-J path (nlls_model_eval -> K1 on the fp64 tensor cores) on that slice
+    tens = run(lsq_gna_parallel, p0[sl], y[sl], fused=False, ftol=0., ptol=0., gtol=0., max_iter=Kg)
+    assert rel_err(tens[-1], alone[-1]) <= 1e-9
