@@ -93,7 +93,7 @@ def test_compiled_wide_model_runs_the_tensor_core_fused_kernel_like_the_builtin(
     from torchimize_b200.models import MultiEMGModel, compile_model
     from test_gpu_multi_emg import multi_emg_batch
     clone = compile_model('namespace nlls { template <typename T> struct UserModel : MultiEmgModel<T, 2> {}; }\n', 'emg2_clone')
-    assert clone.n_params == (8,) and clone.fused_solvers == ('gn', 'lm')
+    assert clone.n_params == (8,) and clone.fused_solvers == ('gn', 'lm', 'gd')
     builtin = MultiEMGModel(2)
     p0, t, y, _ = multi_emg_batch(16, 2, 1024, 4, torch.float64, C=2)
     w = torch.ones(2, dtype=torch.float64, device=DEV)

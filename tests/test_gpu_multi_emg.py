@@ -36,7 +36,7 @@ def test_multi_emg_eval_matches_the_oracle_callables(K):
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize('solver', ['lma', 'gna'])
+@pytest.mark.parametrize('solver', ['lma', 'gna', 'gda'])
 @pytest.mark.parametrize('K', [2, 3, 4])
 def test_multi_emg_solves_match_the_oracle_fp64(solver, K):
     from oracle import nlls_oracle as O, models as M
@@ -46,7 +46,8 @@ def test_multi_emg_solves_match_the_oracle_fp64(solver, K):
     p0, t, y, gt = multi_emg_batch(12, K, 1024, 5, torch.float64)
     kw = dict(ftol=1e-8, ptol=1e-8, gtol=1e-8, max_iter=30)
     model = MultiEMGModel(K)
-    ours = lsq_lma_parallel if solver == 'lma' else lsq_gna_parallel
+    from torchimize_b200.functions import gradient_descent_parallel
+    ours = dict(lma=lsq_lma_parallel, gna=lsq_gna_parallel, gda=gradient_descent_parallel)[solver]
     ref = getattr(O, solver)(p0.clone(), M.multi_emg_cost, M.multi_emg_jac, args=(t, y), **kw)
     for fused in (True, False):                                   # tensor-core fused kernel / materialised J + K1
         p = p0.clone().to(DEV)
@@ -96,18 +97,19 @@ def test_multi_emg_tensor_core_fused_normal_equations_match_the_oracle(K, C, dn)
 
 
 @pytest.mark.gpu
-def test_multi_emg_gd_takes_the_tensor_path_and_the_abi_says_what_exists():
+def test_multi_emg_two_pass_lm_takes_the_tensor_path_and_the_abi_says_what_exists():
     from torchimize_b200 import _lib
     from torchimize_b200.models import MultiEMGModel, fused_model_of
     model = MultiEMGModel(4)
-    assert fused_model_of(model.cost, model.jac, 'gn') is model and fused_model_of(model.cost, model.jac, 'lm') is model
-    assert fused_model_of(model.cost, model.jac, 'gd') is None    # gradient_descent_parallel: nlls_model_eval + K1
+    for key in ('gn', 'lm', 'gd'):
+        assert fused_model_of(model.cost, model.jac, key) is model
+    assert fused_model_of(model.cost, model.jac, 'lm2') is None   # two-pass LM schedule: nlls_model_eval + K1
     p0, t, y, _ = multi_emg_batch(2, 4, 64, 1, torch.float64)
     g = torch.empty(2, 16, dtype=torch.float64, device=DEV)
     H = torch.empty(2, 16, 16, dtype=torch.float64, device=DEV)
     st = torch.empty(2, 4, dtype=torch.float64, device=DEV)
     w = torch.ones(1, dtype=torch.float64, device=DEV)
     pd, td, yd = p0.to(DEV), t.to(DEV), y.to(DEV)
-    with pytest.raises(_lib.NllsError, match='only nlls_model_eval'):
-        _lib.call('nlls_model_normal_eq_gda', _lib.MODEL_MULTI_EMG, _lib.F64, _lib.ptr(pd), 16, _lib.ptr(td), _lib.ptr(yd), 64, 0,
-                  _lib.ptr(w), 1, 2, 1, 64, None, None, _lib.ptr(g), _lib.ptr(H), _lib.ptr(st), None, _lib.stream_ptr())
+    with pytest.raises(_lib.NllsError, match='no two-pass'):
+        _lib.call('nlls_model_cost_stat', _lib.MODEL_MULTI_EMG, _lib.F64, _lib.ptr(pd), 16, _lib.ptr(td), _lib.ptr(yd), 64, 0,
+                  2, 1, 64, _lib.ptr(st), None, _lib.stream_ptr())

@@ -1308,12 +1308,18 @@ __device__ __forceinline__ void dmma_884_acc(double& d0, double& d1, double a, d
                : "+d"(d0), "+d"(d1) : "d"(a), "d"(b));
 }
 
-template <typename T, typename Model, int NW, int MINB>
+// GDA = true: gradient_descent_parallel's cost-summed tall system (gda:134-139): the tile rows are j = 2 s1 k rounded in T
+// (s1 = sum_c w_c r_c), unscaled in the MMA; g64 = sum_n j f_s with f_s = sum_c w_c r_c^2; outputs fp64; fA / fB are the
+// ping-pong buffers of f_s [B,N]; stats = {0, sum (f_s,prev - f_s)^2, sum f_s^2, 0}.
+template <typename T, typename Model, int NW, int MINB, bool GDA = false>
 __global__ void __launch_bounds__(NW * 32, MINB)
 k_model_normal_eq_mma(const T* __restrict__ p, const T* __restrict__ x, const T* __restrict__ y, long long ybs, long long ycs,
-                      const T* __restrict__ w, int wlen, long long B, int C, int N, T* fA, T* fB, T* __restrict__ gout,
-                      T* __restrict__ Hout, double* __restrict__ stats, const nlls_ctrl* ctrl,
+                      const T* __restrict__ w, int wlen, long long B, int C, int N, T* fA, T* fB, void* __restrict__ gout_,
+                      void* __restrict__ Hout_, double* __restrict__ stats, const nlls_ctrl* ctrl,
                       const unsigned char* __restrict__ sel) {
+  using TO = typename std::conditional<GDA, double, T>::type;
+  TO* __restrict__ gout = reinterpret_cast<TO*>(gout_);
+  TO* __restrict__ Hout = reinterpret_cast<TO*>(Hout_);
   if (is_done(ctrl)) return;
   constexpr int P = Model::P, NB = 2, PP = 16, RW = PP * PP + PP + 2, TPB = NW * 32, ROWD = 20;
   static_assert(P <= PP, "tensor-core fused kernel: P <= 16 (tile columns past P are zero)");
@@ -1331,8 +1337,9 @@ k_model_normal_eq_mma(const T* __restrict__ p, const T* __restrict__ x, const T*
     T* f_out = (it & 1) ? fB : fA;
     const T* f_prev = (it > 0 && fA) ? ((it & 1) ? fA : fB) : nullptr;
     if (sel) { const bool s1 = sel[b] != 0; f_out = s1 ? fA : fB; f_prev = s1 ? fB : fA; }
-    if (f_out) f_out += b * (long long)C * N;
-    if (f_prev) f_prev += b * (long long)C * N;
+    const long long fstride = GDA ? (long long)N : (long long)C * N;   // f [B,C,N] / f_s [B,N]
+    if (f_out) f_out += b * fstride;
+    if (f_prev) f_prev += b * fstride;
     Model M;
     M.load(p + b * P);
     double Ht[3][2], Gt[NB];
@@ -1340,7 +1347,8 @@ k_model_normal_eq_mma(const T* __restrict__ p, const T* __restrict__ x, const T*
     for (int i = 0; i < 3; ++i) Ht[i][0] = Ht[i][1] = 0.0;
     Gt[0] = Gt[1] = 0.0;
     double sd = 0.0, sq = 0.0;
-    for (int c = 0; c < C; ++c) csum[c * TPB + tid] = 0.0;
+    if (!GDA)
+      for (int c = 0; c < C; ++c) csum[c * TPB + tid] = 0.0;
     for (int bt = warp; bt < NBATCH; bt += NW) {
       const int n = (bt << 5) + lane;
       const bool live = n < N;
@@ -1351,20 +1359,37 @@ k_model_normal_eq_mma(const T* __restrict__ p, const T* __restrict__ x, const T*
       if (live) {
         M.eval(ld_cached(x + n), m, kk);
         const T* yb = y + b * ybs + n;
-        for (int c = 0; c < C; ++c) {
-          const T wc = w[wlen == 1 ? 0 : c];
-          const T r = ld_cached(yb + c * ycs) - m;
-          const T fv = mul_rn(r, r);
-          if (f_out) stg_stream(f_out + (long long)c * N + n, fv);
-          if (f_prev) { const T d = ldg_stream(f_prev + (long long)c * N + n) - fv; sd = fma((double)d, (double)d, sd); }
-          sq = fma((double)fv, (double)fv, sq);
-          csum[c * TPB + tid] += (double)fv;
-          const T wf = wc * fv;
-          s2 += wf;
-          s3 = fma(wf, r, s3);
+        if constexpr (GDA) {
+          T s1 = T(0), fs = T(0);
+          for (int c = 0; c < C; ++c) {
+            const T wc = w[wlen == 1 ? 0 : c];
+            const T r = ld_cached(yb + c * ycs) - m;
+            s1 = fma(wc, r, s1);
+            fs = fma(wc, r * r, fs);                          // gda:136
+          }
+          if (f_out) f_out[n] = fs;
+          if (f_prev) { const T d = ldg_stream(f_prev + n) - fs; sd = fma((double)d, (double)d, sd); }
+          sq = fma((double)fs, (double)fs, sq);
+          const T c2 = T(2) * s1;
+#pragma unroll
+          for (int i = 0; i < P; ++i) kk[i] = c2 * kk[i];     // gda:137: the cost-summed Jacobian row, rounded in T
+          s3 = fs;
+        } else {
+          for (int c = 0; c < C; ++c) {
+            const T wc = w[wlen == 1 ? 0 : c];
+            const T r = ld_cached(yb + c * ycs) - m;
+            const T fv = mul_rn(r, r);
+            if (f_out) stg_stream(f_out + (long long)c * N + n, fv);
+            if (f_prev) { const T d = ldg_stream(f_prev + (long long)c * N + n) - fv; sd = fma((double)d, (double)d, sd); }
+            sq = fma((double)fv, (double)fv, sq);
+            csum[c * TPB + tid] += (double)fv;
+            const T wf = wc * fv;
+            s2 += wf;
+            s3 = fma(wf, r, s3);
+          }
         }
       }
-      const double s2d = (double)(T(4) * s2), s3d = (double)(T(2) * s3);
+      const double s2d = GDA ? 1.0 : (double)(T(4) * s2), s3d = GDA ? (double)s3 : (double)(T(2) * s3);
 #pragma unroll
       for (int i = 0; i < PP; i += 2) {
         double2 v;
@@ -1378,7 +1403,7 @@ k_model_normal_eq_mma(const T* __restrict__ p, const T* __restrict__ x, const T*
         const int row = 4 * u + k;
         const double2 v = *reinterpret_cast<const double2*>(tile + row * ROWD + NB * gi);
         const double s2k = __shfl_sync(0xffffffffu, s2d, row), s3k = __shfl_sync(0xffffffffu, s3d, row);
-        const double a0 = v.x * s2k, a1 = v.y * s2k;
+        const double a0 = GDA ? v.x : v.x * s2k, a1 = GDA ? v.y : v.y * s2k;
         dmma_884_acc(Ht[0][0], Ht[0][1], a0, v.x);      // block (0,0)
         dmma_884_acc(Ht[1][0], Ht[1][1], a0, v.y);      // block (0,1)
         dmma_884_acc(Ht[2][0], Ht[2][1], a1, v.y);      // block (1,1)
@@ -1416,17 +1441,17 @@ k_model_normal_eq_mma(const T* __restrict__ p, const T* __restrict__ x, const T*
       double sacc = 0.0;
 #pragma unroll
       for (int ww = 0; ww < NW; ++ww) sacc += red[ww * RW + off];
-      Hout[b * P * P + e] = (T)sacc;
+      Hout[b * P * P + e] = (TO)sacc;
     }
     if (tid < P) {
       double sacc = 0.0;
 #pragma unroll
       for (int ww = 0; ww < NW; ++ww) sacc += red[ww * RW + PP * PP + tid];
-      gout[b * P + tid] = (T)sacc;
+      gout[b * P + tid] = (TO)sacc;
     }
     if (warp == NW - 1) {
       double tot = 0.0;
-      for (int c = 0; c < C; ++c) {
+      for (int c = 0; c < (GDA ? 0 : C); ++c) {
         double sacc = 0.0;
 #pragma unroll
         for (int ww = 0; ww < NW; ++ww) sacc += csum[c * TPB + ww * 32 + lane];
@@ -1739,22 +1764,25 @@ static int run_op(Op op, const ModelArgs& a) {
   return NLLS_E_MODEL;
 }
 
-// models with 6 < P <= 16: materialising kernel + the tensor-core fused normal equations (GN and speculative LM);
-// no fused GD / two-pass trial-cost kernels (gradient_descent_parallel takes the tensor path for them)
+// models with 6 < P <= 16: materialising kernel + the tensor-core fused normal equations (GN, speculative LM, GD);
+// no two-pass trial-cost kernel
 template <typename T, typename Model>
 static int run_wide(Op op, const ModelArgs& a, const char* name) {
   if (op == OP_EVAL) return launch_eval<T, Model>(a);
-  if (op == OP_NEQ) {
+  if (op == OP_NEQ || op == OP_NEQ_GDA) {
     constexpr int RW = 16 * 16 + 16 + 2;
+    const bool gda = op == OP_NEQ_GDA;
     auto go = [&](auto kern, int NWv) {
       const int TPB = NWv * 32;
       const size_t smem = ((size_t)NWv * RW + (size_t)NWv * 32 * 20 + (size_t)a.C * TPB) * 8;
       if (smem > 200 * 1024) { set_error("fused model path: too many costs (C=%d)", a.C); return (int)NLLS_E_SHAPE; }
       const int grid = grid_for(kern, TPB, smem, a.B);
       kern<<<grid, TPB, smem, a.st>>>((const T*)a.p, (const T*)a.x, (const T*)a.y, a.ybs, a.ycs, (const T*)a.w, a.wlen, a.B,
-                                      a.C, a.N, (T*)a.fA, (T*)a.fB, (T*)a.g, (T*)a.H, a.stats, a.ctrl, a.sel);
-      return check_launch("nlls_model_normal_eq(mma)");
+                                      a.C, a.N, (T*)a.fA, (T*)a.fB, gda ? (void*)a.g64 : a.g, gda ? (void*)a.H64 : a.H, a.stats,
+                                      a.ctrl, a.sel);
+      return check_launch(gda ? "nlls_model_normal_eq_gda(mma)" : "nlls_model_normal_eq(mma)");
     };
+    if (gda) return go(k_model_normal_eq_mma<T, Model, 4, 6, true>, 4);
     switch (fused_variant()) {                               // tuning hook (occupancy against registers)
 #ifndef NLLS_USER_MODEL_HEADER
       case 1: return go(k_model_normal_eq_mma<T, Model, 4, 5>, 4);   // 96 registers, 20 warps/SM: 6.08 ms at cfg-4
@@ -1766,7 +1794,7 @@ static int run_wide(Op op, const ModelArgs& a, const char* name) {
       default: return go(k_model_normal_eq_mma<T, Model, 4, 6>, 4);
     }
   }
-  set_error("%s (P=%d): only nlls_model_eval, nlls_model_normal_eq and nlls_model_lm_trial exist for P > 6", name, Model::P);
+  set_error("%s (P=%d): no two-pass trial-cost kernel (nlls_model_cost_stat) for P > 6; use nlls_model_lm_trial", name, Model::P);
   return NLLS_E_MODEL;
 }
 

@@ -89,10 +89,10 @@ class MultiEMGModel(FusedModel):
     """Sum of ``n_peaks`` (2..4) EMG peaks, p = [alpha_1, mu_1, sigma_1, eta_1, ...] (P = 4 n_peaks; SURVEY.md §8d, the
     large-P workload of cfg-4).  Gauss-Newton and Levenberg-Marquardt run the tensor-core fused kernel
     (k_model_normal_eq_mma: the model is evaluated once per sample and the per-warp 32 x 16 tile of k rows is reduced
-    with fp64 DMMA; J is never materialised); gradient_descent_parallel, the two-pass LM schedule and ``fused=False``
-    take the tensor path (``nlls_model_eval`` + K1, also on the fp64 tensor cores for P > 8)."""
+    with fp64 DMMA; J is never materialised), so does gradient_descent_parallel (cost-summed rows); the two-pass LM
+    schedule and ``fused=False`` take the tensor path (``nlls_model_eval`` + K1, also on the fp64 tensor cores for P > 8)."""
     model_id = _lib.MODEL_MULTI_EMG
-    fused_solvers = ('gn', 'lm')
+    fused_solvers = ('gn', 'lm', 'gd')
 
     def __init__(self, n_peaks=4, n_costs=None):
         super().__init__(n_costs)
@@ -108,8 +108,8 @@ class CompiledModel(FusedModel):
     def __init__(self, lib, n_params, name, n_costs=None):
         super().__init__(n_costs)
         self.lib, self.n_params, self.name = lib, (int(n_params),), name
-        if int(n_params) > 6:                  # tensor-core fused kernel: GN and speculative LM only (like MultiEMGModel)
-            self.fused_solvers = ('gn', 'lm')
+        if int(n_params) > 6:                  # tensor-core fused kernel: no two-pass LM schedule (like MultiEMGModel)
+            self.fused_solvers = ('gn', 'lm', 'gd')
 
     def __repr__(self):
         return f'CompiledModel({self.name!r}, P={self.n_params[0]})'
