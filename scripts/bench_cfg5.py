@@ -22,7 +22,7 @@ from bench import make_batch                                        # noqa: E402
 from torchimize_b200 import _lib                                    # noqa: E402
 from torchimize_b200.functions import lsq_gna_parallel, lsq_lma_parallel   # noqa: E402
 from torchimize_b200.models import EMGModel                         # noqa: E402
-from torchimize_b200.sharding import shard_bounds, gather_results   # noqa: E402
+from torchimize_b200.sharding import shard_bounds, gather_results, solve_sharded   # noqa: E402
 
 
 def main():
@@ -32,6 +32,8 @@ def main():
     ap.add_argument('--dtypes', default='f32,f64')
     ap.add_argument('--solvers', default='gn,lm')
     ap.add_argument('--reps', type=int, default=2)
+    ap.add_argument('--mode', default='local', choices=['local', 'exact'],
+                    help="exact: all-reduce the 32-byte batch-global sums every iteration (sharding.solve_sharded)")
     args = ap.parse_args()
     world = int(os.environ.get('WORLD_SIZE', '1'))
     rank = int(os.environ.get('RANK', '0'))
@@ -76,7 +78,11 @@ def main():
                     a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
                     l0 = _lib.launches
                     a.record()
-                    out = solver(p, emg.cost, emg.jac, args=(t, y), wvec=w, ftol=1e-8, ptol=1e-8, gtol=1e-8, **kw)
+                    if args.mode == 'exact' and world > 1:
+                        out, _ = solve_sharded(solver, p, emg.cost, emg.jac, args=(t, y), wvec=w, mode='exact', gather=False,
+                                               ftol=1e-8, ptol=1e-8, gtol=1e-8, **kw)
+                    else:
+                        out = solver(p, emg.cost, emg.jac, args=(t, y), wvec=w, ftol=1e-8, ptol=1e-8, gtol=1e-8, **kw)
                     b.record()
                     torch.cuda.synchronize()
                     ms = a.elapsed_time(b)
@@ -113,7 +119,7 @@ def main():
                                   'chunks_per_gpu': n_chunks, 'iterations': it, 'ms': ms, 'solve_ms_rank0': solve_ms, 'gather_ms_rank0': gather_ms, 'problems_per_s': args.B / (ms * 1e-3),
                                   'problem_iters_per_s': args.B * it / (ms * 1e-3),
                                   'whole_solve_GBps_per_gpu': alg / (ms * 1e-3) / 1e9, 'frac_of_measured_hbm': alg / (ms * 1e-3) / 1e9 / peak,
-                                  'gpu_launches_rank0': launches, 'finite': ok, 'scaling': 'strong'}), flush=True)
+                                  'gpu_launches_rank0': launches, 'finite': ok, 'scaling': 'strong', 'mode': args.mode}), flush=True)
             del finals, full
             torch.cuda.empty_cache()
     if world > 1:
