@@ -136,6 +136,14 @@ int nlls_gd_update(int dtype, void* p, const double* g64, const double* H64, con
  * multi-GPU exact run).  */
 int nlls_iter_end(nlls_ctrl* ctrl, int solver, double ftol, void* stream);
 
+/* nlls_iter_end for a batch sharded over the GPUs of one box in "exact" mode (lma:110,118, gna:88, gda:76,84 see the
+ * WHOLE batch): sums ctrl->red over the ranks through peer-mapped mailboxes (NVLink P2P stores + stamp, no collective
+ * library call) and then decides like nlls_iter_end.  mailboxes: device array of `world` pointers, entry r = rank r's
+ * mailbox of 2*world*8 doubles (zero-initialised symmetric memory, mapped into this process); epoch: a per-solve
+ * counter, equal on every rank.  Every rank has to launch it once per iteration. */
+int nlls_iter_end_peer(nlls_ctrl* ctrl, int solver, double ftol, void* const* mailboxes, int rank, int world,
+                       long long epoch, void* stream);
+
 /* ---- single-problem solvers (torchimize/functions/single/*.py: lma_fun_single.py:81,99; gna:81; gda:78) ----------
  * Residual statistics of ONE problem over a vector of any length, spread over the whole GPU: block k writes
  * out[2k] = partial sum_i a[i]^2 and out[2k+1] = partial sum_i (b[i]-a[i])^2 (0 when b is NULL), fp64;

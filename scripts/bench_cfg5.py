@@ -32,7 +32,7 @@ def main():
     ap.add_argument('--dtypes', default='f32,f64')
     ap.add_argument('--solvers', default='gn,lm')
     ap.add_argument('--reps', type=int, default=2)
-    ap.add_argument('--mode', default='local', choices=['local', 'exact'],
+    ap.add_argument('--mode', default='local', choices=['local', 'exact', 'exact-peer'],
                     help="exact: all-reduce the 32-byte batch-global sums every iteration (sharding.solve_sharded)")
     args = ap.parse_args()
     world = int(os.environ.get('WORLD_SIZE', '1'))
@@ -78,8 +78,8 @@ def main():
                     a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
                     l0 = _lib.launches
                     a.record()
-                    if args.mode == 'exact' and world > 1:
-                        out, _ = solve_sharded(solver, p, emg.cost, emg.jac, args=(t, y), wvec=w, mode='exact', gather=False,
+                    if args.mode != 'local' and world > 1:
+                        out, _ = solve_sharded(solver, p, emg.cost, emg.jac, args=(t, y), wvec=w, mode=args.mode, gather=False,
                                                ftol=1e-8, ptol=1e-8, gtol=1e-8, **kw)
                     else:
                         out = solver(p, emg.cost, emg.jac, args=(t, y), wvec=w, ftol=1e-8, ptol=1e-8, gtol=1e-8, **kw)

@@ -184,3 +184,19 @@ def _w_exact_gpu(rank, world, name, dn, path):
 @pytest.mark.parametrize('name', ['lma_lev', 'gna', 'gda'])
 def test_exact_mode_two_ranks_match_full_batch_reference(name, path):
     _spawn(_w_exact_gpu, name, 'f64', path)
+
+
+@pytest.mark.gpu
+def test_exact_peer_mode_matches_single_gpu_bit_for_bit_when_two_gpus_are_present():
+    """mode='exact-peer' (nlls_iter_end_peer: the 32-byte exchange over NVLink peer memory by our own kernel) against
+    mode='exact' (NCCL) and a single-GPU run: scripts/peer_exact_check.py under torchrun; needs >= 2 GPUs on the box."""
+    import subprocess
+    import sys
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip('needs two GPUs on one box')
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, '-m', 'torch.distributed.run', '--nnodes=1', '--nproc-per-node', '2', '--master-addr',
+                        '127.0.0.1', '--master-port', '29533', os.path.join(root, 'scripts', 'peer_exact_check.py')],
+                       capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0 and 'PEER EXACT CHECK OK' in r.stdout, r.stdout[-2000:] + r.stderr[-2000:]

@@ -32,6 +32,7 @@ SIGNATURES = {
     'nlls_gn_update': [_i, _vp, _vp, _vp, _vp, _d, _d, _d, _d, _i, _ll, _i, _vp, _vp, _vp, _vp],
     'nlls_gd_update': [_i, _vp, _vp, _vp, _vp, _d, _d, _d, _d, _i, _ll, _i, _vp, _vp, _vp, _vp],
     'nlls_iter_end': [_vp, _i, _d, _vp],
+    'nlls_iter_end_peer': [_vp, _i, _d, _vp, _i, _i, _ll, _vp],
     'nlls_sumsq_partials': [],
     'nlls_sumsq': [_i, _vp, _vp, _ll, _vp, _vp],
     'nlls_model_eval': [_i, _i, _vp, _i, _vp, _vp, _ll, _ll, _ll, _i, _i, _vp, _vp, _vp, _vp],

@@ -370,6 +370,55 @@ __global__ void k_iter_end(nlls_ctrl* ctrl, int solver, double ftol) {
   ctrl->red[0] = ctrl->red[1] = ctrl->red[2] = ctrl->red[3] = 0.0;
 }
 
+// Multi-GPU "exact" mode without a collective library call: the batch-global stop test needs the SUM over the ranks of
+// the four fp64 reductions of ONE iteration (32 bytes).  Every rank owns a mailbox in peer-mapped (symmetric) memory,
+// [2 parities][world][8 doubles]; thread t of this one-block kernel stores this rank's sums and then a stamp straight into
+// rank t's mailbox over NVLink (P2P stores, data -> __threadfence_system -> stamp), then spins on the stamp of rank t in
+// its OWN mailbox, reads that rank's sums, and thread 0 adds them in rank order (identical bits on every rank) before the
+// usual decision.  Slots alternate with the iteration parity: a rank can run at most one iteration ahead of a peer,
+// because it needs that peer's stamp of the previous iteration to get there.  The stamp carries a per-solve epoch so
+// that a slot left over from an earlier solve can never match.  A peer that does not answer within ~2 s traps.
+__global__ void k_iter_end_peer(nlls_ctrl* ctrl, int solver, double ftol, double* const* __restrict__ mbox, int rank, int world,
+                                long long epoch) {
+  if (ctrl->done) return;
+  const int it = ctrl->iters, par = it & 1, t = threadIdx.x;
+  const double stamp = (double)(epoch * 1048576LL + it + 1);
+  __shared__ double part[4][32];
+  if (t < world) {
+    volatile double* dst = mbox[t] + ((size_t)par * world + rank) * 8;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) dst[i] = ctrl->red[i];
+    __threadfence_system();
+    dst[4] = stamp;
+    volatile double* src = mbox[rank] + ((size_t)par * world + t) * 8;
+    const long long t0 = clock64();
+    while (src[4] != stamp)
+      if (clock64() - t0 > 4000000000LL) __trap();
+    __threadfence_system();
+#pragma unroll
+    for (int i = 0; i < 4; ++i) part[i][t] = src[i];
+  }
+  __syncthreads();
+  if (t != 0) return;
+  double red[4] = {0.0, 0.0, 0.0, 0.0};
+  for (int r = 0; r < world; ++r)
+#pragma unroll
+    for (int i = 0; i < 4; ++i) red[i] += part[i][r];
+  bool done;
+  if (solver == NLLS_SOLVER_LM) {
+    const bool gate = red[1] > 0.0;
+    done = (gate ? red[0] : red[2]) == 0.0;
+  } else if (solver == NLLS_SOLVER_GD) {
+    const bool fcon = (it > 0) && (red[2] < ftol * ftol * red[3]);
+    done = fcon || red[0] == 0.0;
+  } else {
+    done = red[0] == 0.0;
+  }
+  ctrl->iters = it + 1;
+  ctrl->done = done ? 1 : 0;
+  ctrl->red[0] = ctrl->red[1] = ctrl->red[2] = ctrl->red[3] = 0.0;
+}
+
 // =========================================================== warp-cooperative solve, 8 < P <= 32
 // One warp per problem, lane i owns row i of the (damped) matrix in REGISTERS.  Left-looking
 // Cholesky with fully unrolled static register indices; L[j][k] reaches the other lanes by a
@@ -760,6 +809,14 @@ extern "C" int nlls_iter_end(nlls_ctrl* ctrl, int solver, double ftol, void* str
   if (!ctrl) { set_error("nlls_iter_end: NULL ctrl"); return NLLS_E_NULL; }
   k_iter_end<<<1, 1, 0, (cudaStream_t)stream>>>(ctrl, solver, ftol);
   return check_launch("nlls_iter_end");
+}
+
+extern "C" int nlls_iter_end_peer(nlls_ctrl* ctrl, int solver, double ftol, void* const* mailboxes, int rank, int world,
+                                  long long epoch, void* stream) {
+  if (!ctrl || !mailboxes) { set_error("nlls_iter_end_peer: NULL pointer"); return NLLS_E_NULL; }
+  if (world < 1 || world > 32 || rank < 0 || rank >= world) { set_error("nlls_iter_end_peer: rank %d of %d", rank, world); return NLLS_E_SHAPE; }
+  k_iter_end_peer<<<1, 32, 0, (cudaStream_t)stream>>>(ctrl, solver, ftol, (double* const*)mailboxes, rank, world, epoch);
+  return check_launch("nlls_iter_end_peer");
 }
 
 extern "C" int nlls_lm_update_spec(int dtype, void* p, const void* h, void* g, void* H, const void* g_t, const void* H_t,

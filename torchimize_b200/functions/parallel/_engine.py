@@ -170,6 +170,8 @@ def solve(solver, p, function, jac_function, args, wvec, ftol, ptol, gtol, max_i
         return []
     if reduce_hook is None:
         reduce_hook = _default_reduce_hook
+    if getattr(reduce_hook, 'peer', None) is not None:
+        reduce_hook.peer.epoch += 1                          # one epoch per solve, in step on every rank
     work_p = p if p.is_contiguous() else p.contiguous()
     ws = Workspace(work_p, wvec, solver)
     # 'lm' = speculative schedule (nlls_model_lm_trial), 'lm2' = two-pass schedule (needs nlls_model_cost_stat)
@@ -196,6 +198,14 @@ def solve(solver, p, function, jac_function, args, wvec, ftol, ptol, gtol, max_i
             _lib.call('nlls_lm_update', code, _lib.ptr(work_p), _lib.ptr(ws.h), _lib.ptr(ws.g), _lib.ptr(ws.u),
                       _lib.ptr(ws.v), _lib.ptr(ws.stats), _lib.ptr(ws.stat_h), meth, float(lm['rho1']), float(lm['rho2']),
                       float(lm['beta']), float(lm['gama']), ftol, ptol, gtol, B, P, k_hist_ptr, None, ctrl, st())
+        iter_end()
+
+    def iter_end():
+        """closes the iteration; multi-GPU exact mode: NCCL all-reduce of the sums, or the peer-memory kernel"""
+        peer = getattr(reduce_hook, 'peer', None)
+        if peer is not None:
+            _lib.call('nlls_iter_end_peer', ctrl, solver, ftol, _lib.ptr(peer.ptrs), peer.rank, peer.world, peer.epoch, st())
+            return
         if reduce_hook is not None:
             reduce_hook(ws.ctrl[2:6])
         _lib.call('nlls_iter_end', ctrl, solver, ftol, st())
@@ -236,9 +246,7 @@ def solve(solver, p, function, jac_function, args, wvec, ftol, ptol, gtol, max_i
                           _lib.ptr(g_t), _lib.ptr(H_t), _lib.ptr(ws.u), _lib.ptr(ws.v), _lib.ptr(ws.stats), _lib.ptr(stats_t),
                           _lib.ptr(sel), meth, float(lm['rho1']), float(lm['rho2']), float(lm['beta']), float(lm['gama']),
                           ftol, ptol, gtol, B, P, hp, None, ctrl, st())
-                if reduce_hook is not None:
-                    reduce_hook(ws.ctrl[2:6])
-                _lib.call('nlls_iter_end', ctrl, solver, ftol, st())
+                iter_end()
             launched += group
             ws.post_flags()
             done, iters, sing = ws.poll_flags(lag=1)

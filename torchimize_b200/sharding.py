@@ -8,6 +8,9 @@ Problems are independent, so B is split into contiguous shards, one process per 
                 (32 bytes) once per iteration, so the global break (lma:118, gna:88, gda:84), the
                 "any rho > 0" gate (lma:110) and GD's batch-global fcon (gda:76) see the whole
                 batch and iteration counts match a single-device run of the reference.
+  mode='exact-peer'  the same exchange done by our own kernel (nlls_iter_end_peer): every rank stores its
+                32 bytes + a stamp straight into the peers' mailboxes over NVLink (symmetric memory) and
+                sums what it received — no collective library call inside the iteration.
 """
 import torch
 import torch.distributed as dist
@@ -32,6 +35,35 @@ def make_reduce_hook(group=None):
     return hook
 
 
+class PeerExchange:
+    """Peer-mapped mailboxes for nlls_iter_end_peer: the 32-byte exchange of exact mode done by our own kernel with NVLink
+    P2P stores instead of an NCCL all-reduce per iteration (one launch instead of two, no collective launch latency).
+    Needs every rank of `group` on one NVLink/NVSwitch box (torch symmetric memory over CUDA IPC)."""
+
+    def __init__(self, group=None):
+        import torch.distributed._symmetric_memory as symm_mem
+        group = dist.group.WORLD if group is None else group
+        self.rank, self.world = dist.get_rank(group), dist.get_world_size(group)
+        if self.world > 32:
+            raise ValueError('PeerExchange: at most 32 ranks')
+        dev = torch.device('cuda', torch.cuda.current_device())
+        self.buf = symm_mem.empty(2 * self.world * 8, dtype=torch.float64, device=dev)
+        self.buf.zero_()
+        self.handle = symm_mem.rendezvous(self.buf, group=group.group_name)
+        self.ptrs = torch.tensor([int(q) for q in self.handle.buffer_ptrs], dtype=torch.int64, device=dev)
+        self.epoch = 0
+        torch.cuda.synchronize()
+        dist.barrier(group)                                  # every mailbox is zeroed before anybody writes into a peer
+
+
+def make_peer_hook(group=None):
+    """Hook for _engine.solve(reduce_hook=...) that selects the peer-memory iteration end (see PeerExchange)."""
+    def hook(red):                                           # never called: the engine launches nlls_iter_end_peer instead
+        raise RuntimeError('peer hook is driven by the engine')
+    hook.peer = PeerExchange(group)
+    return hook
+
+
 def gather_results(p_local, B_total, group=None):
     """All-gather the per-rank [B_r, P] finals into the full [B_total, P] tensor on every rank
     (one collective; shards may differ by one row, so they are padded to the largest)."""
@@ -49,6 +81,9 @@ def gather_results(p_local, B_total, group=None):
     return torch.cat(parts, dim=0)
 
 
+_peer_hooks = {}
+
+
 def solve_sharded(solver_fn, p_local, function, jac_function=None, args=(), wvec=None, mode='local',
                   group=None, B_total=None, gather=True, **kw):
     """Run one of the drop-in solvers on this rank's shard and (optionally) gather the finals.
@@ -57,9 +92,16 @@ def solve_sharded(solver_fn, p_local, function, jac_function=None, args=(), wvec
     p_local / args: this rank's shard (use shard()/shard_bounds() to cut them)
     returns (coeffs_list_local, p_full or None)"""
     from .functions.parallel import _engine
-    if mode not in ('local', 'exact'):
-        raise ValueError("mode must be 'local' or 'exact'")
-    hook = make_reduce_hook(group) if (mode == 'exact' and dist.is_initialized() and dist.get_world_size(group) > 1) else None
+    if mode not in ('local', 'exact', 'exact-peer'):
+        raise ValueError("mode must be 'local', 'exact' or 'exact-peer'")
+    multi = dist.is_initialized() and dist.get_world_size(group) > 1
+    hook = None
+    if mode == 'exact' and multi:
+        hook = make_reduce_hook(group)
+    elif mode == 'exact-peer' and multi:                     # exact semantics, exchange by nlls_iter_end_peer (NVLink P2P)
+        if group not in _peer_hooks:
+            _peer_hooks[group] = make_peer_hook(group)
+        hook = _peer_hooks[group]
     if hook is None:
         coeffs = solver_fn(p_local, function, jac_function, args=args, wvec=wvec, **kw)
     else:
