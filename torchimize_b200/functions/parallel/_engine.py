@@ -180,12 +180,22 @@ def solve(solver, p, function, jac_function, args, wvec, ftol, ptol, gtol, max_i
     st = _lib.stream_ptr
     B, P, code = ws.B, ws.P, ws.code
     ctrl = _lib.ptr(ws.ctrl)
+    state = lm.get('state') if solver == LM else None
     if solver == LM:
-        ws.u.fill_(lm['tau'])                    # u = tau * max diag(I)   (lma:77-78, Q8)
-        ws.v.fill_(2.)
-        ws.dscale[:, 0] = 1.
-        ws.dscale[:, 1] = 0.
         meth = _lib.LM_LEVENBERG if lm['meth'] == 'lev' else _lib.LM_MARQUARDT
+        if state:                                # warm restart: the damping state of a previous call
+            for name in ('u', 'v', 'dscale'):
+                src, dst = state.get(name), getattr(ws, name)
+                if not isinstance(src, torch.Tensor) or src.shape != dst.shape or src.device != dst.device:
+                    raise _lib.NllsError(f"state['{name}'] must be a {tuple(dst.shape)} tensor on {dst.device}")
+                dst.copy_(src)
+            if state.get('meth', lm['meth']) != lm['meth']:
+                raise _lib.NllsError("state was produced with another damping method ('meth')")
+        else:
+            ws.u.fill_(lm['tau'])                # u = tau * max diag(I)   (lma:77-78, Q8)
+            ws.v.fill_(2.)
+            ws.dscale[:, 0] = 1.
+            ws.dscale[:, 1] = 0.
 
     def update(k_hist_ptr):
         if solver == GN:
@@ -314,6 +324,8 @@ def solve(solver, p, function, jac_function, args, wvec, ftol, ptol, gtol, max_i
         warnings.warn('Condition number of at least one Hessian is infinite giving NaNs. Consider a step rate l<1.')
     if work_p is not p:
         p.copy_(work_p)                                     # Q1: the caller's tensor ends as the final iterate
+    if state is not None:                                   # caller-owned dict, updated in place like p
+        state.update(u=ws.u.clone(), v=ws.v.clone(), dscale=ws.dscale.clone(), meth=lm['meth'], iterations=int(iters))
     return ws.snapshots(iters)
 
 

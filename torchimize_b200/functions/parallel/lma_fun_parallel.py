@@ -22,7 +22,7 @@ def lsq_lma_parallel(
         beta: float = 2,
         gama: float = 3,
         max_iter: int = 100,
-        *, fused: bool = True,
+        *, fused: bool = True, state: dict = None,
 ) -> List[torch.Tensor]:
     """Batched Levenberg-Marquardt on the B200 core.
 
@@ -30,6 +30,10 @@ def lsq_lma_parallel(
     return value (list of per-iteration B x P snapshots; p is updated in place) as the reference.
     ``meth='lev'`` is Levenberg/Nielsen damping, anything else Marquardt (lma:83-88).
     ``fused`` (keyword-only, not in the reference): allow the in-kernel model evaluation when
-    ``function``/``jac_function`` are the methods of a torchimize_b200.models.FusedModel."""
+    ``function``/``jac_function`` are the methods of a torchimize_b200.models.FusedModel.
+    ``state`` (keyword-only, not in the reference): a caller-owned dict for warm restarts. An empty dict
+    starts as the reference does (u = tau, v = 2) and receives the damping state (u, v, Marquardt scale) at return;
+    passing it to the next call continues from that state, so that k calls of max_iter = n walk the same iterates as one
+    call of max_iter = k n (as long as no call stopped early)."""
     return _engine.solve(_engine.LM, p, function, jac_function, args, wvec, ftol, ptol, gtol, max_iter,
-                         lm=dict(tau=tau, meth=meth, rho1=rho1, rho2=rho2, beta=beta, gama=gama), fused=fused)
+                         lm=dict(tau=tau, meth=meth, rho1=rho1, rho2=rho2, beta=beta, gama=gama, state=state), fused=fused)
