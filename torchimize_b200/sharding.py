@@ -95,6 +95,9 @@ def solve_sharded(solver_fn, p_local, function, jac_function=None, args=(), wvec
     if mode not in ('local', 'exact', 'exact-peer'):
         raise ValueError("mode must be 'local', 'exact' or 'exact-peer'")
     multi = dist.is_initialized() and dist.get_world_size(group) > 1
+    if multi and mode != 'local' and (p_local.shape[0] == 0 or (B_total is not None and B_total < dist.get_world_size(group))):
+        # a rank without problems returns before the first iteration and would leave the others waiting in the exchange
+        raise ValueError(f"mode='{mode}' needs at least one problem on every rank")
     hook = None
     if mode == 'exact' and multi:
         hook = make_reduce_hook(group)
