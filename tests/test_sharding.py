@@ -134,6 +134,12 @@ def _w_solve_sharded(rank, world):
     assert out.shape == (B, 3)
     with pytest.raises(ValueError):
         sharding.solve_sharded(fake_solver, mine, None, mode='bogus')
+    # exact modes refuse a batch that leaves a rank without problems (it would never enter the exchange)
+    for mode in ('exact', 'exact-peer'):
+        with pytest.raises(ValueError):
+            sharding.solve_sharded(fake_solver, sharding.shard(torch.zeros(1, 3), world, rank).clone(), None, mode=mode, B_total=1)
+    _, out = sharding.solve_sharded(fake_solver, sharding.shard(torch.zeros(1, 3), world, rank).clone(), None, mode='local', B_total=1)
+    assert out.shape == (1, 3)
 
 
 def test_solve_sharded_host_logic_gloo():
