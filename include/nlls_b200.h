@@ -27,7 +27,7 @@
 extern "C" {
 #endif
 
-#define NLLS_B200_ABI_VERSION 1
+#define NLLS_B200_ABI_VERSION 2   /* 2: the fused kernels keep the model value m [B,N] between iterations, not f [B,C,N] */
 
 enum { NLLS_F32 = 0, NLLS_F64 = 1 };
 
@@ -164,14 +164,17 @@ int nlls_model_eval(int model, int dtype, const void* p, int P, const void* x, c
                     void* f_out, void* J_out /*nullable*/, const nlls_ctrl* ctrl, void* stream);
 
 /* nlls_model_normal_eq: K4+K1 fused — evaluates the model once per (b,n), loops the costs,
- * never materialises J.  Same outputs as nlls_normal_eq.  f_pp[2] are two [B,C,N] ping-pong
- * buffers: iteration k reads f_prev from f_pp[(k+1)&1] (when k>0) and writes f to f_pp[k&1]
- * with k = ctrl->iters (k = 0 when ctrl == NULL).  f_pp0 may be NULL to skip the f traffic
- * (then stats[1] = 0). */
+ * never materialises J.  Same outputs as nlls_normal_eq.  m_pp[2] are two [B,N] ping-pong
+ * buffers of the MODEL VALUE m(p; x): iteration k reads m_prev from m_pp[(k+1)&1] (when k>0)
+ * and writes m to m_pp[k&1] with k = ctrl->iters (k = 0 when ctrl == NULL).  The previous
+ * residuals that fcon needs (lma:110, gna:80) are rebuilt in-kernel as
+ * f_prev[b,c,n] = (y[b,c,n] - m_prev[b,n])^2 — the same two roundings that produced them, so
+ * stats[1] is bit-identical to the sum over stored residuals at s*N*(C+2) bytes per
+ * problem-iteration instead of 3*s*C*N.  m_pp0 may be NULL to skip that traffic (then stats[1] = 0). */
 int nlls_model_normal_eq(int model, int dtype, const void* p, int P, const void* x, const void* y,
                          long long y_bstride, long long y_cstride,
                          const void* wvec, int wlen, long long B, int C, int N,
-                         void* f_pp0, void* f_pp1, void* g, void* H, double* stats,
+                         void* m_pp0, void* m_pp1, void* g, void* H, double* stats,
                          const nlls_ctrl* ctrl, void* stream);
 
 /* Speculative Levenberg-Marquardt trial evaluation (fused path): ONE pass at the trial point p + h that yields
@@ -180,13 +183,13 @@ int nlls_model_normal_eq(int model, int dtype, const void* p, int P, const void*
  *                  sum (f_cur - f_t)^2, sum f_t^2  (the NEXT iteration's fcon sums, lma:110), 0 }
  *   g_t, H_t   = normal equations at the trial point (what the next iteration uses if the step is accepted;
  *                a rejected step keeps the current g, H — p did not move — so nothing is recomputed).
- * sel [B] (bytes): problem b's CURRENT residuals f_cur live in (sel[b] ? f_buf1 : f_buf0); the trial residuals
- * f_t are written to the other buffer.  nlls_lm_update_spec flips sel[b] on acceptance.  Same arithmetic, in the
- * same order, as nlls_model_normal_eq at the accepted point: trajectories are bit-identical to the two-pass
- * schedule (nlls_model_normal_eq + nlls_model_cost_stat) at 2/3 of its HBM traffic. */
+ * sel [B] (bytes): the model values m_cur [B,N] at problem b's CURRENT point live in (sel[b] ? m_buf1 : m_buf0)
+ * (f_cur is rebuilt from them and y); the trial values m_t are written to the other buffer.  nlls_lm_update_spec
+ * flips sel[b] on acceptance.  Same arithmetic, in the same order, as nlls_model_normal_eq at the accepted point:
+ * trajectories are bit-identical to the two-pass schedule (nlls_model_normal_eq + nlls_model_cost_stat). */
 int nlls_model_lm_trial(int model, int dtype, const void* p_trial, int P, const void* x, const void* y,
                         long long y_bstride, long long y_cstride, const void* wvec, int wlen,
-                        long long B, int C, int N, void* f_buf0, void* f_buf1, const unsigned char* sel,
+                        long long B, int C, int N, void* m_buf0, void* m_buf1, const unsigned char* sel,
                         void* g_t, void* H_t, double* stats_t, const nlls_ctrl* ctrl, void* stream);
 
 /* K3 for the speculative schedule (lma:100-116, 124-152): as nlls_lm_update, with

@@ -22,3 +22,30 @@ def pytest_collection_modifyitems(config, items):
     for it in items:
         if 'gpu' in it.keywords:
             it.add_marker(skip)
+
+
+@pytest.fixture(scope='session', autouse=True)
+def _report_boundary_flips():
+    """Writes every fp32 iteration-count flip seen by helpers.compare_plist (and how many comparisons could have
+    flipped) to profiles/r02_boundary_flips_{gpu,cpu}.json — north_star: boundary flips are REPORTED.  On the GPU box
+    the same file also lands in gpurun_out/ so that it travels back."""
+    yield
+    import json
+    import torch
+    import helpers
+    if not helpers.COMPARED:
+        return
+    kind = 'gpu' if torch.cuda.is_available() else 'cpu'
+    rec = {'what': 'fp32 iteration-count flips against the reference golden trajectories (tests/helpers.py::compare_plist, '
+                   f'bound +-{helpers.MAX_FLIP}); ours = ' + ('CUDA path' if kind == 'gpu' else 'CPU oracle'),
+           'comparisons': len(helpers.COMPARED), 'flips': helpers.FLIPS, 'compared': helpers.COMPARED}
+    for d in ('profiles', 'gpurun_out'):
+        path = os.path.join(ROOT, d)
+        if d == 'gpurun_out' and kind == 'cpu':
+            continue
+        try:
+            os.makedirs(path, exist_ok=True)
+            with open(os.path.join(path, f'r02_boundary_flips_{kind}.json'), 'w') as f:
+                json.dump(rec, f, indent=1)
+        except OSError:
+            pass

@@ -27,6 +27,9 @@ CASES = {
     'gda':      ('gda', dict(l=1., max_iter=99, **TOL)),
     'gda_l05':  ('gda', dict(l=.5, max_iter=99, **TOL)),
 }
+# mirrors tests/golden/make_golden_cfg5.py::CASES5 (cfg-5 shape: C=5, N=1024, P=4; max_iter as scripts/bench_cfg5.py)
+CASES5 = {'lma_lev': ('lma', dict(meth='lev', max_iter=40, **TOL)),
+          'gna': ('gna', dict(l=1., max_iter=80, **TOL))}
 PLAIN = {'gna_plain': ('gna_plain', dict(l=.1, max_iter=25)),
          'gda_plain': ('gda_plain', dict(l=.1, max_iter=25))}
 
@@ -69,25 +72,44 @@ def rel_err(a, b):
     return float((num / den).max())
 
 
-def compare_plist(got, want, dn, what, allow_boundary=False):
+# Iteration-count flips (north_star: "identical convergence iteration counts except at tolerance boundaries, which are
+# reported"): only fp32 cases may flip, by at most MAX_FLIP iterations, and every flip is recorded here; conftest.py
+# writes the list to profiles/r02_boundary_flips*.json at the end of the session (an empty list is a result too).
+MAX_FLIP = 1
+FLIPS = []
+COMPARED = []          # every (case, dtype, ours, reference) that went through compare_plist with allow_boundary
+
+
+def compare_plist(got, want, dn, what, allow_boundary=False, max_flip=MAX_FLIP):
     """got: list/stack of [B,P] snapshots; want: golden [K,B,P].  Checks iteration count and
-    EVERY snapshot (not only the last)."""
+    EVERY snapshot (not only the last).  allow_boundary (fp32 only): the counts may differ by at most
+    max_flip — a stop test that sits within rounding noise of its tolerance; the flip is recorded, the
+    common prefix is held to RTOL_MID and the TRUE finals (last snapshot of each run) to RTOL."""
     want = torch.as_tensor(want)
     got = torch.stack(list(got)) if not torch.is_tensor(got) else got
     got = got.cpu()
-    if got.shape[0] != want.shape[0]:
-        msg = f'{what}: iteration count {got.shape[0]} != reference {want.shape[0]}'
-        if allow_boundary:
-            print('BOUNDARY FLIP:', msg)
-            k = min(got.shape[0], want.shape[0])
-            got, want = got[:k], want[:k]
-        else:
+    k_got, k_want = got.shape[0], want.shape[0]
+    if allow_boundary:
+        COMPARED.append(dict(case=what, dtype=dn, ours=k_got, reference=k_want))
+    fin_g, fin_w = got[-1], want[-1]
+    if k_got != k_want:
+        msg = f'{what}: iteration count {k_got} != reference {k_want}'
+        if not allow_boundary:
             raise AssertionError(msg)
+        assert abs(k_got - k_want) <= max_flip, msg + f' (more than a +-{max_flip} boundary flip)'
+        print('BOUNDARY FLIP:', msg)
+        k = min(k_got, k_want)
+        FLIPS.append(dict(case=what, dtype=dn, ours=k_got, reference=k_want,
+                          final_rel_err=rel_err(torch.nan_to_num(fin_g.double()), torch.nan_to_num(fin_w.double()))))
+        got, want = got[:k], want[:k]
     finite = torch.isfinite(want)
     assert torch.equal(torch.isfinite(got), finite), f'{what}: finite pattern differs'
-    g = torch.where(finite, got.double(), torch.zeros((), dtype=torch.float64))
-    w = torch.where(finite, want.double(), torch.zeros((), dtype=torch.float64))
-    e = rel_err(g[-1], w[-1])
+    zero = torch.zeros((), dtype=torch.float64)
+    g = torch.where(finite, got.double(), zero)
+    w = torch.where(finite, want.double(), zero)
+    ffin = torch.isfinite(fin_w)
+    assert torch.equal(torch.isfinite(fin_g), ffin), f'{what}: finite pattern of the finals differs'
+    e = rel_err(torch.where(ffin, fin_g.double(), zero), torch.where(ffin, fin_w.double(), zero))
     assert e <= RTOL[dn], f'{what}: final rel err {e:.3e} > {RTOL[dn]:.0e}'
     e_mid = rel_err(g, w)
     assert e_mid <= RTOL_MID[dn], f'{what}: snapshot rel err {e_mid:.3e} > {RTOL_MID[dn]:.0e}'

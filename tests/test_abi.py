@@ -29,9 +29,9 @@ def test_library_exports_every_declared_symbol():
 
 def test_abi_version_and_ctrl_size():
     lib = _lib.load()
-    assert lib.nlls_abi_version() == 1
+    assert lib.nlls_abi_version() == 2
     hdr = open(os.path.join(ROOT, 'include', 'nlls_b200.h')).read()
-    assert '#define NLLS_B200_ABI_VERSION 1' in hdr
+    assert '#define NLLS_B200_ABI_VERSION 2' in hdr
 
     class Ctrl(ctypes.Structure):
         _fields_ = [('done', ctypes.c_int), ('iters', ctypes.c_int), ('singular', ctypes.c_int),

@@ -62,7 +62,8 @@ def test_multi_emg_solves_match_the_oracle_fp64(solver, K):
 @pytest.mark.parametrize('K', [2, 3, 4])
 def test_multi_emg_tensor_core_fused_normal_equations_match_the_oracle(K, C, dn):
     """nlls_model_normal_eq for P = 8|12|16 (k_model_normal_eq_mma: DMMA over the per-warp tile of k rows) against the
-    oracle's newton step on the materialised J, two consecutive iterations (the second reads f_prev), ragged N."""
+    oracle's newton step on the materialised J, two consecutive iterations (the second rebuilds f_prev from the stored
+    model values m [B,N]), ragged N."""
     from oracle import nlls_oracle as O, models as M
     from torchimize_b200 import _lib
     dt = torch.float64 if dn == 'f64' else torch.float32
@@ -71,7 +72,7 @@ def test_multi_emg_tensor_core_fused_normal_equations_match_the_oracle(K, C, dn)
     p0, t, y, _ = multi_emg_batch(B, K, N, 9, dt, C=C)
     w = torch.linspace(1., 1.4, C, dtype=dt)
     pd, td, yd, wd = (v.to(DEV) for v in (p0, t, y, w))
-    fpp = torch.zeros(2, B, C, N, dtype=dt, device=DEV)
+    fpp = torch.zeros(2, B, N, dtype=dt, device=DEV)
     g = torch.empty(B, P, dtype=dt, device=DEV)
     H = torch.empty(B, P, P, dtype=dt, device=DEV)
     st = torch.empty(B, 4, dtype=torch.float64, device=DEV)
@@ -88,7 +89,8 @@ def test_multi_emg_tensor_core_fused_normal_equations_match_the_oracle(K, C, dn)
         g0, H0 = O.normal_equations(f, J, w)
         assert float((g.cpu() - g0).abs().max()) <= tol * float(g0.abs().max())
         assert float((H.cpu() - H0).abs().max()) <= tol * float(H0.abs().max())
-        assert float((fpp[it & 1].cpu() - f).abs().max()) <= tol * float(f.abs().max())
+        m0 = M.multi_emg_model(p0 * scale, t)
+        assert float((fpp[it & 1].cpu() - m0).abs().max()) <= tol * float(m0.abs().max())
         assert torch.allclose(st[:, 0].cpu(), O.cost_sum_stat(f).double(), rtol=1e-9 if dn == 'f64' else 1e-3)
         assert torch.allclose(st[:, 2].cpu(), (f.double() ** 2).sum((1, 2)), rtol=1e-9 if dn == 'f64' else 1e-3)
         if f_prev is not None:

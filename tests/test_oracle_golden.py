@@ -7,7 +7,7 @@ import pytest
 import torch
 
 from conftest import GOLDEN
-from helpers import CASES, PLAIN, DT, CHAOTIC_PREFIX, load, compare_plist, rel_err
+from helpers import CASES, CASES5, PLAIN, DT, CHAOTIC_PREFIX, load, compare_plist, rel_err
 from oracle import nlls_oracle as O
 from oracle import models as M
 
@@ -69,6 +69,19 @@ def test_skewgauss_cases(skew, name, dn, P):
     pre = f'P{P}_'
     args = (torch.as_tensor(skew[pre + 'x']).to(dt), torch.as_tensor(skew[pre + 'y']).to(dt))
     _run_case(skew, name, dn, M.skewgauss_cost, M.skewgauss_jac, args, prefix=pre)
+
+
+@pytest.mark.parametrize('dn', ['f64', 'f32'])
+@pytest.mark.parametrize('name', list(CASES5))
+def test_cfg5_shape_cases(name, dn):
+    """BASELINE.json configs[4] shape (C=5, N=1024, P=4): the 16-problem golden batch of make_golden_cfg5.py."""
+    gold = load('cfg5')
+    dt = DT[dn]
+    fun, jac, args = _emg_args(gold, dt)
+    solver, kw = CASES5[name]
+    p = torch.as_tensor(gold['p0']).to(dt).clone()
+    tr = getattr(O, solver)(p, fun, jac, args=args, wvec=torch.as_tensor(gold['wvec']).to(dt), **kw)
+    compare_plist(tr.p_list, gold[f'{name}__{dn}__plist'], dn, f'cfg5 {name}__{dn}', allow_boundary=(dn == 'f32'))
 
 
 @pytest.mark.parametrize('dn', ['f64', 'f32'])

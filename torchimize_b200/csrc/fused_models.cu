@@ -7,8 +7,14 @@
 //     f_c = r_c^2,  J_c = 2 r_c k
 //     g   = sum_n k   * (2 sum_c w_c r_c^3)
 //     H   = sum_n k k^T (4 sum_c w_c r_c^2)
-// (newton_parallel.py:40-43 applied to tests/unit_test_parallel.py:53-65,105-118).  HBM traffic per
-// iteration: y once, f_prev once (read), f once (write) — 3*s*C*N bytes per problem.
+// (newton_parallel.py:40-43 applied to tests/unit_test_parallel.py:53-65,105-118).
+//
+// The stop test fcon (lma:110, gna:80) needs sum (f_prev - f)^2 sample by sample.  f_prev[b,c,n] was produced one
+// iteration earlier as mul_rn(y_c - m_prev, y_c - m_prev): it depends on the data y_c (in the stage anyway) and ONE
+// scalar m_prev[b,n] shared by all C costs.  The kernels therefore keep the MODEL VALUE m [B,N] between iterations
+// (ping-pong), not the residuals f [B,C,N], and rebuild f_prev with one subtraction and one multiplication per
+// (c,n) — the same two roundings that produced it, so the sums are bit-identical to those of stored residuals.
+// HBM traffic per problem-iteration: y once (s*Cy*N), m_prev read + m written (2*s*N): s*N*(C+2) instead of 3*s*C*N.
 #include <cstdlib>
 #include <type_traits>
 #include "models.cuh"
@@ -38,16 +44,16 @@ __device__ __forceinline__ bool aligned_to_dev(const void* p, size_t a) { return
 template <typename T, typename Model, int TPB, int S>
 __global__ void __launch_bounds__(TPB)
 k_model_normal_eq(const T* __restrict__ p, const T* __restrict__ x, const T* __restrict__ y, long long ybs,
-                  long long ycs, const T* __restrict__ w, int wlen, long long B, int C, int N, T* fA, T* fB,
+                  long long ycs, const T* __restrict__ w, int wlen, long long B, int C, int N, T* mA, T* mB,
                   T* __restrict__ g, T* __restrict__ H, double* __restrict__ stats, const nlls_ctrl* ctrl,
                   const unsigned char* __restrict__ sel) {
   if (is_done(ctrl)) return;
   constexpr int P = Model::P, NW = TPB / 32, NH = Tri<P>::N, V = P + NH + 2;
   const int it = iter_index(ctrl);
   // sel == NULL: buffers alternate with the iteration parity.  sel != NULL (speculative LM trial evaluation):
-  // problem b's current residuals live in (sel[b] ? fB : fA) and the trial residuals go to the other buffer.
-  T* f_out = (it & 1) ? fB : fA;
-  const T* f_prev = (it > 0 && fA) ? ((it & 1) ? fA : fB) : nullptr;
+  // problem b's current model values live in (sel[b] ? mB : mA) and the trial values go to the other buffer.
+  T* m_out = (it & 1) ? mB : mA;
+  const T* m_prev = (it > 0 && mA) ? ((it & 1) ? mA : mB) : nullptr;
   extern __shared__ double smem[];
   double* red = smem;                  // [NW][V]
   double* sfc = smem + NW * V;         // [C][TPB] per-thread per-cost sums of f
@@ -55,7 +61,7 @@ k_model_normal_eq(const T* __restrict__ p, const T* __restrict__ x, const T* __r
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
 
   for (long long b = blockIdx.x; b < B; b += gridDim.x) {
-    if (sel) { const bool sb = sel[b] != 0; f_prev = sb ? fB : fA; f_out = sb ? fA : fB; }
+    if (sel) { const bool sb = sel[b] != 0; m_prev = sb ? mB : mA; m_out = sb ? mA : mB; }
     Model M;
     M.load(p + b * P);
     RowAcc<T, P> acc;
@@ -64,29 +70,34 @@ k_model_normal_eq(const T* __restrict__ p, const T* __restrict__ x, const T* __r
     for (int c = 0; c < C; ++c) sfc[c * TPB + tid] = 0.0;
     const T* yb = y + b * ybs;
     for (int n0 = 0; n0 < N; n0 += TPB * S) {
-      T m[S], k[S][P], s2[S], s3[S];
+      T m[S], mp[S], k[S][P], s2[S], s3[S];
 #pragma unroll
       for (int i = 0; i < S; ++i) {
         const int n = n0 + i * TPB + tid;
         M.eval(ld_cached(x + min(n, N - 1)), m[i], k[i]);
         s2[i] = T(0);
         s3[i] = T(0);
+        mp[i] = T(0);
+        if (n < N) {
+          if (m_prev) mp[i] = ldg_stream(m_prev + b * N + n);
+          if (m_out) stg_stream(m_out + b * N + n, m[i]);
+        }
       }
 #pragma unroll 2
       for (int c = 0; c < C; ++c) {
         const T wc = w[wlen == 1 ? 0 : c];
         const T* yc = yb + c * ycs;
-        const long long seg = (b * C + c) * (long long)N;
         double sfl = 0.0;
 #pragma unroll
         for (int i = 0; i < S; ++i) {
           const int n = n0 + i * TPB + tid;
           if (n < N) {
-            const T r = ld_cached(yc + n) - m[i];
+            const T yv = ld_cached(yc + n);
+            const T r = yv - m[i];
             const T fv = mul_rn(r, r);
-            if (f_out) stg_stream(f_out + seg + n, fv);
-            if (f_prev) {
-              const T d = ldg_stream(f_prev + seg + n) - fv;
+            if (m_prev) {                                    // f_prev rebuilt from the stored model value (bit-identical)
+              const T rp = yv - mp[i];
+              const T d = mul_rn(rp, rp) - fv;
               sd = fma((double)d, (double)d, sd);
             }
             sq = fma((double)fv, (double)fv, sq);
@@ -214,11 +225,11 @@ struct TileRing {
 };
 
 // ------------------------------------------------------------------ fused normal equations, bulk-copy staged
-// Same arithmetic as k_model_normal_eq, but the data rows y[b,c,n0:n0+TN] and f_prev[b,c,n0:n0+TN]
+// Same arithmetic as k_model_normal_eq, but the data rows y[b,c,n0:n0+TN] and the row m_prev[b,n0:n0+TN]
 // of a tile are brought into shared memory by 1-D bulk async copies (cp.async.bulk -> UBLKCP,
 // completion on one mbarrier per stage) issued NSTAGE tiles ahead by one elected thread, across
 // problem boundaries.  The r01a profile of the direct kernel showed 73 % of its stalls on the
-// scoreboard of the y / f_prev loads (profiles/r01a_fused_baseline.txt): the loads sat in the
+// scoreboard of the y / previous-residual loads (profiles/r01a_fused_baseline.txt): the loads sat in the
 // dependent chain of each sample.  Here the bytes in flight per SM no longer depend on registers
 // or occupancy.  TN = TPB * S samples per tile.  One __syncthreads per tile (stage hand-back) and
 // one per problem (cross-warp sums, double-buffered); the per-problem warp sums use the
@@ -226,7 +237,7 @@ struct TileRing {
 template <typename T, typename Model, int TPB, int S, int NSTAGE>
 __global__ void __launch_bounds__(TPB)
 k_model_normal_eq_staged(const T* __restrict__ p, const T* __restrict__ x, const T* __restrict__ y, long long ybs,
-                         long long ycs, const T* __restrict__ w, int wlen, long long B, int C, int N, T* fA, T* fB,
+                         long long ycs, const T* __restrict__ w, int wlen, long long B, int C, int N, T* mA, T* mB,
                          T* __restrict__ g, T* __restrict__ H, double* __restrict__ stats, const nlls_ctrl* ctrl,
                          const unsigned char* __restrict__ sel) {
   if (is_done(ctrl)) return;
@@ -234,11 +245,11 @@ k_model_normal_eq_staged(const T* __restrict__ p, const T* __restrict__ x, const
   constexpr int VP = Pow2Ceil<V>::value, OWN = 32 / VP;      // transposed reduction: lane L owns value L / OWN
   static_assert(V <= 32, "model with too many parameters for the transposed reduction");
   const int it = iter_index(ctrl);
-  T* f_out = (it & 1) ? fB : fA;
-  const T* f_prev = (it > 0 && fA) ? ((it & 1) ? fA : fB) : nullptr;
-  const bool has_prev = f_prev != nullptr || sel != nullptr;  // sel: per-problem buffer roles (see k_model_normal_eq)
+  T* m_out = (it & 1) ? mB : mA;
+  const T* m_prev = (it > 0 && mA) ? ((it & 1) ? mA : mB) : nullptr;
+  const bool has_prev = m_prev != nullptr || sel != nullptr;  // sel: per-problem buffer roles (see k_model_normal_eq)
   const int Cy = (ycs == 0) ? 1 : C;                         // one shared data row, or one per cost
-  const int stage_elems = (Cy + C) * TN;                     // [Cy][TN] data rows then [C][TN] f_prev rows
+  const int stage_elems = (Cy + 1) * TN;                     // [Cy][TN] data rows then [TN] previous model values
   extern __shared__ __align__(128) unsigned char smem_raw[];
   T* ring = reinterpret_cast<T*>(smem_raw);
   size_t off = (size_t)NSTAGE * stage_elems * sizeof(T);
@@ -265,13 +276,10 @@ k_model_normal_eq_staged(const T* __restrict__ p, const T* __restrict__ x, const
     const unsigned bytes = (unsigned)rows * (unsigned)sizeof(T);
     T* dst = ring + (size_t)pst * stage_elems;
     uint64_t* bar = &bars[pst];
-    mbar_expect_tx(bar, bytes * (unsigned)(Cy + (has_prev ? C : 0)));
+    mbar_expect_tx(bar, bytes * (unsigned)(Cy + (has_prev ? 1 : 0)));
     const T* src = y + pb * ybs + pn0;
     for (int c = 0; c < Cy; ++c, src += ycs, dst += TN) bulk_g2s(dst, src, bytes, bar);
-    if (has_prev) {
-      const T* ps = (sel ? (psel ? fB : fA) : f_prev) + pb * (long long)C * N + pn0;
-      for (int c = 0; c < C; ++c, ps += N, dst += TN) bulk_g2s(dst, ps, bytes, bar);
-    }
+    if (has_prev) bulk_g2s(dst, (sel ? (psel ? mB : mA) : m_prev) + pb * (long long)N + pn0, bytes, bar);
     pn0 += TN;
     if (pn0 >= N) {
       pn0 = 0;
@@ -296,8 +304,8 @@ k_model_normal_eq_staged(const T* __restrict__ p, const T* __restrict__ x, const
     double sd = 0.0, sq = 0.0;
     double* my_sfc = sfc + (size_t)pbuf * C * TPB + tid;
     for (int c = 0; c < C; ++c) my_sfc[c * TPB] = 0.0;
-    if (sel) f_out = sel[b] ? fA : fB;
-    T* fo_b = f_out ? f_out + b * (long long)C * N : nullptr;
+    if (sel) m_out = sel[b] ? mA : mB;
+    T* mo_b = m_out ? m_out + b * (long long)N : nullptr;
     for (int n0 = 0; n0 < N; n0 += TN) {
       T m[S], k[S][P], s2[S], s3[S];
 #pragma unroll
@@ -307,23 +315,30 @@ k_model_normal_eq_staged(const T* __restrict__ p, const T* __restrict__ x, const
         s2[i] = T(0);
         s3[i] = T(0);
       }
+      if (mo_b) {
+#pragma unroll
+        for (int i = 0; i < S; ++i)
+          if (n0 + i * TPB + tid < N) stg_stream(mo_b + n0 + i * TPB + tid, m[i]);
+      }
       mbar_wait(&bars[st], ph);
       const T* yc = ring + (size_t)st * stage_elems + tid;
-      const T* pc = yc + Cy * TN;
       const int ystep = (Cy == 1) ? 0 : TN;
-      T* fo = fo_b ? fo_b + n0 + tid : nullptr;
+      T mp[S];
+#pragma unroll
+      for (int i = 0; i < S; ++i) mp[i] = has_prev ? yc[Cy * TN + i * TPB] : T(0);   // rows past N: stale, masked below
 #pragma unroll 2
-      for (int c = 0; c < C; ++c, yc += ystep, pc += TN) {
+      for (int c = 0; c < C; ++c, yc += ystep) {
         const T wc = w[wlen == 1 ? 0 : c];
         double sfl = 0.0;
 #pragma unroll
         for (int i = 0; i < S; ++i) {
           if (n0 + i * TPB + tid < N) {
-            const T r = yc[i * TPB] - m[i];
+            const T yv = yc[i * TPB];
+            const T r = yv - m[i];
             const T fv = mul_rn(r, r);
-            if (fo) stg_stream(fo + i * TPB, fv);
-            if (has_prev) {
-              const T d = pc[i * TPB] - fv;
+            if (has_prev) {                                  // f_prev rebuilt from the stored model value (bit-identical)
+              const T rp = yv - mp[i];
+              const T d = mul_rn(rp, rp) - fv;
               sd = fma((double)d, (double)d, sd);
             }
             sq = fma((double)fv, (double)fv, sq);
@@ -334,7 +349,6 @@ k_model_normal_eq_staged(const T* __restrict__ p, const T* __restrict__ x, const
           }
         }
         my_sfc[c * TPB] += sfl;
-        if (fo) fo += N;
       }
 #pragma unroll
       for (int i = 0; i < S; ++i)
@@ -396,7 +410,7 @@ k_model_normal_eq_staged(const T* __restrict__ p, const T* __restrict__ x, const
 // ------------------------------------------------------------------ fused normal equations, staged, 128-bit lanes
 // Same tiles, same bulk-copy producer and same per-problem epilogue as k_model_normal_eq_staged, but a thread owns
 // VEC = 16 / sizeof(T) ADJACENT samples of a tile (4 fp32, 2 fp64) instead of S samples TPB apart: one 128-bit LDS per
-// data row and per f_prev row, one 128-bit STG of f and one 128-bit load of the abscissa per thread, tile and cost
+// data row, one for the previous model values, one 128-bit STG of m and one 128-bit load of the abscissa per thread and tile
 // (the r01d profile of the fp32 kernel counted ~70 thread instructions per (cost, sample), a third of them address
 // arithmetic, per-sample bounds predicates and fp32->fp64 conversions: profiles/r01d_fused_weak.txt, cfg2gnf32).
 // Bulk-copy eligibility already makes N a multiple of VEC, so ONE predicate per thread and tile covers the tail.
@@ -431,7 +445,7 @@ template <> struct Lane16<double> {
 template <typename T, typename Model, int TPB, int NSTAGE>
 __global__ void __launch_bounds__(TPB, 512 / TPB)
 k_model_normal_eq_vec(const T* __restrict__ p, const T* __restrict__ x, const T* __restrict__ y, long long ybs,
-                      long long ycs, const T* __restrict__ w, int wlen, long long B, int C, int N, T* fA, T* fB,
+                      long long ycs, const T* __restrict__ w, int wlen, long long B, int C, int N, T* mA, T* mB,
                       T* __restrict__ g, T* __restrict__ H, double* __restrict__ stats, const nlls_ctrl* ctrl,
                       const unsigned char* __restrict__ sel) {
   if (is_done(ctrl)) return;
@@ -439,11 +453,11 @@ k_model_normal_eq_vec(const T* __restrict__ p, const T* __restrict__ x, const T*
   constexpr int VP = Pow2Ceil<V>::value, OWN = 32 / VP;
   static_assert(V <= 32, "model with too many parameters for the transposed reduction");
   const int it = iter_index(ctrl);
-  T* f_out = (it & 1) ? fB : fA;
-  const T* f_prev = (it > 0 && fA) ? ((it & 1) ? fA : fB) : nullptr;
-  const bool has_prev = f_prev != nullptr || sel != nullptr;
+  T* m_out = (it & 1) ? mB : mA;
+  const T* m_prev = (it > 0 && mA) ? ((it & 1) ? mA : mB) : nullptr;
+  const bool has_prev = m_prev != nullptr || sel != nullptr;
   const int Cy = (ycs == 0) ? 1 : C;
-  const int stage_elems = (Cy + C) * TN;
+  const int stage_elems = (Cy + 1) * TN;                     // [Cy][TN] data rows then [TN] previous model values
   extern __shared__ __align__(128) unsigned char smem_raw[];
   T* ring = reinterpret_cast<T*>(smem_raw);
   size_t off = (size_t)NSTAGE * stage_elems * sizeof(T);
@@ -469,13 +483,10 @@ k_model_normal_eq_vec(const T* __restrict__ p, const T* __restrict__ x, const T*
     const unsigned bytes = (unsigned)rows * (unsigned)sizeof(T);
     T* dst = ring + (size_t)pst * stage_elems;
     uint64_t* bar = &bars[pst];
-    mbar_expect_tx(bar, bytes * (unsigned)(Cy + (has_prev ? C : 0)));
+    mbar_expect_tx(bar, bytes * (unsigned)(Cy + (has_prev ? 1 : 0)));
     const T* src = y + pb * ybs + pn0;
     for (int c = 0; c < Cy; ++c, src += ycs, dst += TN) bulk_g2s(dst, src, bytes, bar);
-    if (has_prev) {
-      const T* ps = (sel ? (psel ? fB : fA) : f_prev) + pb * (long long)C * N + pn0;
-      for (int c = 0; c < C; ++c, ps += N, dst += TN) bulk_g2s(dst, ps, bytes, bar);
-    }
+    if (has_prev) bulk_g2s(dst, (sel ? (psel ? mB : mA) : m_prev) + pb * (long long)N + pn0, bytes, bar);
     pn0 += TN;
     if (pn0 >= N) {
       pn0 = 0;
@@ -501,8 +512,8 @@ k_model_normal_eq_vec(const T* __restrict__ p, const T* __restrict__ x, const T*
     double sd = 0.0, sq = 0.0;
     double* my_sfc = sfc + (size_t)pbuf * C * TPB + tid;
     for (int c = 0; c < C; ++c) my_sfc[c * TPB] = 0.0;
-    if (sel) f_out = sel[b] ? fA : fB;
-    T* fo_b = f_out ? f_out + b * (long long)C * N : nullptr;
+    if (sel) m_out = sel[b] ? mA : mB;
+    T* mo_b = m_out ? m_out + b * (long long)N : nullptr;
     for (int n0 = 0; n0 < N; n0 += TN) {
       const int n = n0 + tid * VEC;
       const bool live = n < N;                               // N % VEC == 0: the whole lane group is in or out
@@ -512,28 +523,25 @@ k_model_normal_eq_vec(const T* __restrict__ p, const T* __restrict__ x, const T*
         Lane16<T>::ldg(x + n, xv);
 #pragma unroll
         for (int j = 0; j < VEC; ++j) { M.eval(xv[j], m[j], k[j]); s2[j] = T(0); s3[j] = T(0); }   // overlaps the wait below
+        if (mo_b) Lane16<T>::stg(mo_b + n, m);
       }
       mbar_wait(&bars[st], ph);
       if (live) {
         const T* yc = ring + (size_t)st * stage_elems + tid * VEC;
-        const T* pc = yc + Cy * TN;
-        T* fo = fo_b ? fo_b + n : nullptr;
         T sdt = T(0), sqt = T(0);
-        T yv[VEC];
+        T yv[VEC], mp[VEC];
+        if (has_prev) Lane16<T>::lds(yc + Cy * TN, mp);
         Lane16<T>::lds(yc, yv);
 #pragma unroll 2
-        for (int c = 0; c < C; ++c, pc += TN) {
+        for (int c = 0; c < C; ++c) {
           const T wc = w[wlen == 1 ? 0 : c];
           if (c > 0 && ystep) { yc += ystep; Lane16<T>::lds(yc, yv); }
           T r[VEC], fv[VEC];
 #pragma unroll
           for (int j = 0; j < VEC; ++j) { r[j] = yv[j] - m[j]; fv[j] = mul_rn(r[j], r[j]); }
-          if (fo) { Lane16<T>::stg(fo, fv); fo += N; }
-          if (has_prev) {
-            T pv[VEC];
-            Lane16<T>::lds(pc, pv);
+          if (has_prev) {                                    // f_prev rebuilt from the stored model value (bit-identical)
 #pragma unroll
-            for (int j = 0; j < VEC; ++j) { const T d = pv[j] - fv[j]; sdt = fma(d, d, sdt); }
+            for (int j = 0; j < VEC; ++j) { const T rp = yv[j] - mp[j]; const T d = mul_rn(rp, rp) - fv[j]; sdt = fma(d, d, sdt); }
           }
           T sfl = T(0);
 #pragma unroll
@@ -613,8 +621,8 @@ k_model_normal_eq_vec(const T* __restrict__ p, const T* __restrict__ x, const T*
 // cross-warp shared-memory reduction.  fp32 keeps its per-block partial sums and the warp reduction in fp32 (the
 // reference sums everything in fp32); the cross-block sums of the statistics stay fp64.
 // MODE: WPP_NEQ normal equations (newton_parallel.py:40-43 fused with the model), WPP_GDA cost-summed tall system
-// (gda:134-139), WPP_COST trial cost (lma:99-100).  prevA/prevB are the ping-pong buffers of f [B,C,N] (NEQ) or of the
-// cost-summed f_s [B,N] (GDA); outg/outH are T (NEQ) or fp64 (GDA).
+// (gda:134-139), WPP_COST trial cost (lma:99-100).  prevA/prevB are the [B,N] ping-pong buffers of the model value m (NEQ:
+// f_prev is rebuilt from it, see the head of this file) or of the cost-summed f_s (GDA); outg/outH are T (NEQ) or fp64 (GDA).
 enum { WPP_NEQ = 0, WPP_GDA = 1, WPP_COST = 2 };
 
 template <typename T, typename Model, int MODE, int SB, int NSTAGE, int NW, bool C1, bool VL = false>
@@ -639,7 +647,7 @@ k_model_wpp(const T* __restrict__ p, const T* __restrict__ x, const T* __restric
   const T* f_prev = (MODE != WPP_COST && it > 0 && prevA) ? ((it & 1) ? prevA : prevB) : nullptr;
   const bool has_prev = f_prev != nullptr || sel != nullptr;  // sel (NEQ only): per-problem buffer roles
   const int Cy = (C1 || ycs == 0) ? 1 : C;
-  const int CP = (MODE == WPP_NEQ) ? C : (MODE == WPP_GDA ? 1 : 0);            // rows of "previous" data per chunk
+  const int CP = (MODE == WPP_COST) ? 0 : 1;                                   // rows of "previous" data per chunk (m or f_s)
   const int stage_elems = (Cy + CP) * CH;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int l0 = VL ? lane * SB : lane;      // a lane's first sample within a block
@@ -659,7 +667,7 @@ k_model_wpp(const T* __restrict__ p, const T* __restrict__ x, const T* __restric
   __syncwarp();
   const long long wid = (long long)blockIdx.x * NW + warp, nwarps = (long long)gridDim.x * NW;
   const int QN = (N + CH - 1) / CH;
-  const long long prev_bs = (MODE == WPP_NEQ) ? (long long)C * N : (long long)N;   // problem stride of prev / f_out
+  const long long prev_bs = (long long)N;                                      // problem stride of prev / f_out
 
   long long fb = wid;                       // producer cursor: next chunk to request
   int fq = 0;
@@ -729,6 +737,16 @@ k_model_wpp(const T* __restrict__ p, const T* __restrict__ x, const T* __restric
           if constexpr (MODE == WPP_COST) m[i] = M.value(xv);
           else M.eval(xv, m[i], k[i]);
         }
+        if constexpr (MODE == WPP_NEQ) {                                      // the model value is what the next iteration reads back
+          if (fo_q) {
+            if constexpr (VL) { if (FULL || j0 + l0 < rows) Lane16<T>::stg(fo_q + j0, m); }
+            else {
+#pragma unroll
+              for (int i = 0; i < SB; ++i)
+                if (FULL || j0 + i * 32 + lane < rows) stg_stream(fo_q + j0 + i * 32, m[i]);
+            }
+          }
+        }
         if (!waited) { mbar_wait(&bars[st], ph); waited = true; }             // first block's model evaluation overlaps the wait
         const T* yc = sy + j0;
         const T* pc = sp + j0;
@@ -781,12 +799,12 @@ k_model_wpp(const T* __restrict__ p, const T* __restrict__ x, const T* __restric
 #pragma unroll
           for (int i = 0; i < SB; ++i) {
             if (FULL || j0 + i * ISTR + l0 < rows) {
-              const T r = (VL ? yl[i] : yc[i * 32]) - m[i];
+              const T yv = VL ? yl[i] : yc[i * 32];
+              const T r = yv - m[i];
               const T fv = mul_rn(r, r);
-              if constexpr (VL) fl[i] = fv;
-              else if (fo) stg_stream(fo + i * 32, fv);
-              if (has_prev) {
-                const T d = (VL ? pl[i] : pc[i * 32]) - fv;
+              if (has_prev) {                                 // f_prev rebuilt from the stored model value (bit-identical)
+                const T rp = yv - (VL ? pl[i] : pc[i * 32]);
+                const T d = mul_rn(rp, rp) - fv;
                 sd_t = fma(d, d, sd_t);
               }
               sq_t = fma(fv, fv, sq_t);
@@ -795,22 +813,25 @@ k_model_wpp(const T* __restrict__ p, const T* __restrict__ x, const T* __restric
               acc.add_scaled(k[i], T(2) * (wf * r), T(4) * wf);
             }
           }
-          if constexpr (VL) { if (fo && (FULL || j0 + l0 < rows)) Lane16<T>::stg(fo, fl); }
         } else {
           T s2[SB], s3[SB];
 #pragma unroll
           for (int i = 0; i < SB; ++i) { s2[i] = T(0); s3[i] = T(0); }
-          for (int c = 0; c < C; ++c, yc += ystep, pc += CH) {
+          T mp[SB];
+#pragma unroll
+          for (int i = 0; i < SB; ++i) mp[i] = has_prev ? pc[i * 32] : T(0);   // rows past the chunk: stale, masked below
+          for (int c = 0; c < C; ++c, yc += ystep) {
             const T wc = w[wlen == 1 ? 0 : c];
             T sfl = T(0);
 #pragma unroll
             for (int i = 0; i < SB; ++i) {
               if (FULL || j0 + i * 32 + lane < rows) {
-                const T r = yc[i * 32] - m[i];
+                const T yv = yc[i * 32];
+                const T r = yv - m[i];
                 const T fv = mul_rn(r, r);
-                if (fo) stg_stream(fo + i * 32, fv);
                 if (has_prev) {
-                  const T d = pc[i * 32] - fv;
+                  const T rp = yv - mp[i];
+                  const T d = mul_rn(rp, rp) - fv;
                   sd_t = fma(d, d, sd_t);
                 }
                 sq_t = fma(fv, fv, sq_t);
@@ -821,7 +842,6 @@ k_model_wpp(const T* __restrict__ p, const T* __restrict__ x, const T* __restric
               }
             }
             sfc[c * 32 + lane] += (double)sfl;
-            if (fo) fo += N;
           }
 #pragma unroll
           for (int i = 0; i < SB; ++i)
@@ -1297,11 +1317,11 @@ k_model_eval(const T* __restrict__ p, const T* __restrict__ x, const T* __restri
 // Multi-peak models (cfg-4: four EMG peaks, P = 16) have too many accumulators for the register-resident kernels above
 // (g and the packed triangle of H would be 152 fp64 values per thread).  Here a warp owns batches of 32 consecutive
 // samples: lane L evaluates sample L once (model value m and k = -dm/dp, all peaks), loops the costs for the residuals
-// (f written, f_prev read, statistics, s2 = 4 sum_c w_c r_c^2, s3 = 2 sum_c w_c r_c^3 as in k_model_normal_eq) and drops
+// (m written, m_prev read and f_prev rebuilt from it, statistics, s2 = 4 sum_c w_c r_c^2, s3 = 2 sum_c w_c r_c^3 as in k_model_normal_eq) and drops
 // its k row into a per-warp shared tile [32][16] (row stride 160 B: conflict-free 128-bit reads).  The 32 x 16 tile is
 // then reduced on the fp64 tensor cores exactly like K1's k_normal_eq_dmma_vec (mma.sync.m8n8k4.f64 -> DMMA): lane
 // (gi, k) reads the two columns {2 gi, 2 gi + 1} of row 4u + k; H += (s2 k) k^T takes 3 DMMAs per 4 rows, g += s3 k
-// two DFMAs.  J [B,C,N,P] (17 GB at cfg-4) is never written or read: per problem-iteration the kernel moves 3 s C N
+// two DFMAs.  J [B,C,N,P] (17 GB at cfg-4) is never written or read: per problem-iteration the kernel moves s N (C + 2)
 // bytes instead of the tensor path's s C N (2 P + 4).
 __device__ __forceinline__ void dmma_884_acc(double& d0, double& d1, double a, double b) {
   asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
@@ -1310,7 +1330,7 @@ __device__ __forceinline__ void dmma_884_acc(double& d0, double& d1, double a, d
 
 // GDA = true: gradient_descent_parallel's cost-summed tall system (gda:134-139): the tile rows are j = 2 s1 k rounded in T
 // (s1 = sum_c w_c r_c), unscaled in the MMA; g64 = sum_n j f_s with f_s = sum_c w_c r_c^2; outputs fp64; fA / fB are the
-// ping-pong buffers of f_s [B,N]; stats = {0, sum (f_s,prev - f_s)^2, sum f_s^2, 0}.
+// [B,N] ping-pong buffers of f_s (GDA) or of the model value m (otherwise); stats = {0, sum (f_s,prev - f_s)^2, sum f_s^2, 0}.
 template <typename T, typename Model, int NW, int MINB, bool GDA = false>
 __global__ void __launch_bounds__(NW * 32, MINB)
 k_model_normal_eq_mma(const T* __restrict__ p, const T* __restrict__ x, const T* __restrict__ y, long long ybs, long long ycs,
@@ -1337,7 +1357,7 @@ k_model_normal_eq_mma(const T* __restrict__ p, const T* __restrict__ x, const T*
     T* f_out = (it & 1) ? fB : fA;
     const T* f_prev = (it > 0 && fA) ? ((it & 1) ? fA : fB) : nullptr;
     if (sel) { const bool s1 = sel[b] != 0; f_out = s1 ? fA : fB; f_prev = s1 ? fB : fA; }
-    const long long fstride = GDA ? (long long)N : (long long)C * N;   // f [B,C,N] / f_s [B,N]
+    const long long fstride = (long long)N;                            // m [B,N] / f_s [B,N]
     if (f_out) f_out += b * fstride;
     if (f_prev) f_prev += b * fstride;
     Model M;
@@ -1375,12 +1395,14 @@ k_model_normal_eq_mma(const T* __restrict__ p, const T* __restrict__ x, const T*
           for (int i = 0; i < P; ++i) kk[i] = c2 * kk[i];     // gda:137: the cost-summed Jacobian row, rounded in T
           s3 = fs;
         } else {
+          if (f_out) stg_stream(f_out + n, m);
+          const T mp = f_prev ? ldg_stream(f_prev + n) : T(0);
           for (int c = 0; c < C; ++c) {
             const T wc = w[wlen == 1 ? 0 : c];
-            const T r = ld_cached(yb + c * ycs) - m;
+            const T yv = ld_cached(yb + c * ycs);
+            const T r = yv - m;
             const T fv = mul_rn(r, r);
-            if (f_out) stg_stream(f_out + (long long)c * N + n, fv);
-            if (f_prev) { const T d = ldg_stream(f_prev + (long long)c * N + n) - fv; sd = fma((double)d, (double)d, sd); }
+            if (f_prev) { const T rp = yv - mp; const T d = mul_rn(rp, rp) - fv; sd = fma((double)d, (double)d, sd); }
             sq = fma((double)fv, (double)fv, sq);
             csum[c * TPB + tid] += (double)fv;
             const T wf = wc * fv;
@@ -1488,7 +1510,7 @@ struct ModelArgs {
   const void *p, *x, *y, *w;
   long long ybs, ycs, B;
   int wlen, C, N;
-  void *fA, *fB, *g, *H;
+  void *fA, *fB, *g, *H;             // fA / fB: [B,N] ping-pong buffers (model value m, or GD's cost-summed f_s)
   double *g64, *H64, *stats, *stat_out;
   void *f_out, *J_out;
   const unsigned char* sel;          // speculative LM: per-problem current-buffer flags (NULL otherwise)
@@ -1514,7 +1536,7 @@ static int launch_staged(const ModelArgs& a) {
   constexpr int P = Model::P, V = P + Tri<P>::N + 2, NW2 = TPB2 / 32, TN = TPB2 * S2, VP = Pow2Ceil<V>::value;
   const size_t es = sizeof(T);
   const int Cy = a.ycs == 0 ? 1 : a.C;
-  const size_t stage = (size_t)(Cy + a.C) * TN * es;
+  const size_t stage = (size_t)(Cy + 1) * TN * es;
   const size_t tail = 16 + 64 + ((size_t)2 * NW2 * VP + (size_t)2 * a.C * TPB2) * 8;
   const bool ok16 = aligned_to(a.y, 16) && (a.ybs * es) % 16 == 0 && (a.ycs * es) % 16 == 0 && ((size_t)a.N * es) % 16 == 0 &&
                     (!a.fA || (aligned_to(a.fA, 16) && aligned_to(a.fB, 16)));
@@ -1541,7 +1563,7 @@ static int launch_vec(const ModelArgs& a) {
   constexpr int P = Model::P, V = P + Tri<P>::N + 2, NW2 = TPB2 / 32, TN = TPB2 * Lane16<T>::VEC, VP = Pow2Ceil<V>::value;
   const size_t es = sizeof(T);
   const int Cy = a.ycs == 0 ? 1 : a.C;
-  const size_t stage = (size_t)(Cy + a.C) * TN * es;
+  const size_t stage = (size_t)(Cy + 1) * TN * es;
   const size_t tail = 16 + 64 + ((size_t)2 * NW2 * VP + (size_t)2 * a.C * TPB2) * 8;
   const bool ok16 = aligned_to(a.y, 16) && aligned_to(a.x, 16) && (a.ybs * es) % 16 == 0 && (a.ycs * es) % 16 == 0 &&
                     ((size_t)a.N * es) % 16 == 0 && (!a.fA || (aligned_to(a.fA, 16) && aligned_to(a.fB, 16)));
@@ -1573,7 +1595,7 @@ static int launch_wpp(const ModelArgs& a) {
   constexpr int NW = 4, SB = 2, NSTAGE = 3;
   const size_t es = sizeof(T);
   const int Cy = a.ycs == 0 ? 1 : a.C;
-  const int CP = MODE == WPP_NEQ ? a.C : (MODE == WPP_GDA ? 1 : 0);
+  const int CP = MODE == WPP_COST ? 0 : 1;
   const bool ok16 = aligned_to(a.y, 16) && (a.ybs * es) % 16 == 0 && (a.ycs * es) % 16 == 0 && ((size_t)a.N * es) % 16 == 0 &&
                     (!a.fA || (aligned_to(a.fA, 16) && aligned_to(a.fB, 16)));
   if (!ok16) return 1;
@@ -1798,8 +1820,10 @@ static int run_wide(Op op, const ModelArgs& a, const char* name) {
   return NLLS_E_MODEL;
 }
 
+// Build-time split (Makefile): NLLS_FUSED_PART == 1 compiles only the fp32 instantiations, NLLS_FUSED_PART == 0 everything
+// else plus the entry points; undefined (plugin build) = one translation unit.
 template <typename T>
-static int run_model(int model, int P, Op op, const ModelArgs& a) {
+int run_model(int model, int P, Op op, const ModelArgs& a) {
 #ifdef NLLS_USER_MODEL_HEADER
   if (model == NLLS_MODEL_USER && P == UserModel<T>::P) {
     if constexpr (UserModel<T>::P <= 6) return run_op<T, UserModel<T>>(op, a);        // register-resident fused kernels
@@ -1820,6 +1844,13 @@ static int run_model(int model, int P, Op op, const ModelArgs& a) {
 #endif
 }
 
+#if defined(NLLS_FUSED_PART) && NLLS_FUSED_PART == 1
+template int run_model<float>(int, int, Op, const ModelArgs&);
+#elif defined(NLLS_FUSED_PART)
+extern template int run_model<float>(int, int, Op, const ModelArgs&);
+#endif
+
+#if !defined(NLLS_FUSED_PART) || NLLS_FUSED_PART == 0
 static int dispatch(int model, int dtype, int P, Op op, const ModelArgs& a) {
   if (dtype != NLLS_F32 && dtype != NLLS_F64) { set_error("dtype %d is not NLLS_F32/NLLS_F64", dtype); return NLLS_E_DTYPE; }
   if (a.B < 0 || a.C < 1 || a.N < 1 || (op <= OP_NEQ_GDA && a.wlen != 1 && a.wlen != a.C)) {
@@ -1831,8 +1862,11 @@ static int dispatch(int model, int dtype, int P, Op op, const ModelArgs& a) {
   return dtype == NLLS_F64 ? run_model<double>(model, P, op, a) : run_model<float>(model, P, op, a);
 }
 
+#endif
+
 }  // namespace nlls
 
+#if !defined(NLLS_FUSED_PART) || NLLS_FUSED_PART == 0
 using namespace nlls;
 
 extern "C" int nlls_model_eval(int model, int dtype, const void* p, int P, const void* x, const void* y, long long y_bstride,
@@ -1847,12 +1881,12 @@ extern "C" int nlls_model_eval(int model, int dtype, const void* p, int P, const
 
 extern "C" int nlls_model_normal_eq(int model, int dtype, const void* p, int P, const void* x, const void* y,
                                     long long y_bstride, long long y_cstride, const void* wvec, int wlen, long long B, int C,
-                                    int N, void* f_pp0, void* f_pp1, void* g, void* H, double* stats, const nlls_ctrl* ctrl,
+                                    int N, void* m_pp0, void* m_pp1, void* g, void* H, double* stats, const nlls_ctrl* ctrl,
                                     void* stream) {
   ModelArgs a{};
   a.p = p; a.x = x; a.y = y; a.w = wvec; a.ybs = y_bstride; a.ycs = y_cstride; a.B = B; a.C = C; a.N = N; a.wlen = wlen;
-  a.fA = f_pp0; a.fB = f_pp1; a.g = g; a.H = H; a.stats = stats; a.ctrl = ctrl; a.st = (cudaStream_t)stream;
-  if (!wvec || !g || !H || !stats || (f_pp0 && !f_pp1)) { set_error("nlls_model_normal_eq: NULL tensor"); return NLLS_E_NULL; }
+  a.fA = m_pp0; a.fB = m_pp1; a.g = g; a.H = H; a.stats = stats; a.ctrl = ctrl; a.st = (cudaStream_t)stream;
+  if (!wvec || !g || !H || !stats || (m_pp0 && !m_pp1)) { set_error("nlls_model_normal_eq: NULL tensor"); return NLLS_E_NULL; }
   return dispatch(model, dtype, P, OP_NEQ, a);
 }
 
@@ -1879,11 +1913,12 @@ extern "C" int nlls_model_cost_stat(int model, int dtype, const void* p_trial, i
 
 extern "C" int nlls_model_lm_trial(int model, int dtype, const void* p_trial, int P, const void* x, const void* y,
                                    long long y_bstride, long long y_cstride, const void* wvec, int wlen, long long B, int C,
-                                   int N, void* f_buf0, void* f_buf1, const unsigned char* sel, void* g_t, void* H_t,
+                                   int N, void* m_buf0, void* m_buf1, const unsigned char* sel, void* g_t, void* H_t,
                                    double* stats_t, const nlls_ctrl* ctrl, void* stream) {
   ModelArgs a{};
   a.p = p_trial; a.x = x; a.y = y; a.w = wvec; a.ybs = y_bstride; a.ycs = y_cstride; a.B = B; a.C = C; a.N = N; a.wlen = wlen;
-  a.fA = f_buf0; a.fB = f_buf1; a.g = g_t; a.H = H_t; a.stats = stats_t; a.sel = sel; a.ctrl = ctrl; a.st = (cudaStream_t)stream;
-  if (!wvec || !g_t || !H_t || !stats_t || !f_buf0 || !f_buf1 || !sel) { set_error("nlls_model_lm_trial: NULL tensor"); return NLLS_E_NULL; }
+  a.fA = m_buf0; a.fB = m_buf1; a.g = g_t; a.H = H_t; a.stats = stats_t; a.sel = sel; a.ctrl = ctrl; a.st = (cudaStream_t)stream;
+  if (!wvec || !g_t || !H_t || !stats_t || !m_buf0 || !m_buf1 || !sel) { set_error("nlls_model_lm_trial: NULL tensor"); return NLLS_E_NULL; }
   return dispatch(model, dtype, P, OP_NEQ, a);
 }
+#endif  // NLLS_FUSED_PART

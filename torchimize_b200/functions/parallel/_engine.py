@@ -230,10 +230,8 @@ def solve(solver, p, function, jac_function, args, wvec, ftol, ptol, gtol, max_i
         if ws.w.numel() not in (1, C):
             raise _lib.NllsError(f'wvec has {ws.w.numel()} entries for {C} costs')
         mid = model.model_id
-        if solver == GD:
-            fpp = torch.empty(2, B, N, dtype=ws.dtype, device=ws.device)
-        else:
-            fpp = torch.empty(2, B, C, N, dtype=ws.dtype, device=ws.device)
+        # [B,N] ping-pong: the model value m (GN, LM: f_prev is rebuilt from it in-kernel) or GD's cost-summed f_s
+        fpp = torch.empty(2, B, N, dtype=ws.dtype, device=ws.device)
         launched, done = 0, False
         spec = solver == LM and SPECULATIVE_LM
         if spec:
@@ -243,7 +241,7 @@ def solve(solver, p, function, jac_function, args, wvec, ftol, ptol, gtol, max_i
             sel = torch.zeros(B, dtype=torch.uint8, device=ws.device)
             _lib.call('nlls_model_normal_eq', mid, code, _lib.ptr(work_p), P, _lib.ptr(x), _lib.ptr(y), ybs, ycs,
                       _lib.ptr(ws.w), ws.w.numel(), B, C, N, _lib.ptr(fpp[0]), _lib.ptr(fpp[1]), _lib.ptr(ws.g),
-                      _lib.ptr(ws.H), _lib.ptr(ws.stats), ctrl, st(), lib=model.lib)             # iteration 0: f(p0) -> fpp[0], sel == 0
+                      _lib.ptr(ws.H), _lib.ptr(ws.stats), ctrl, st(), lib=model.lib)             # iteration 0: m(p0) -> fpp[0], sel == 0
         while spec and launched < max_iter and not done:
             hp = ws.hist_base_ptr(launched, max_iter)
             group = min(check_every, max_iter - launched, ws.hist_room(launched))
