@@ -40,6 +40,8 @@ enum {                       /* negative return codes */
   NLLS_E_ARCH = -6           /* not running on an sm_100 device */
 };
 
+enum { NLLS_CTRL_E_PEER_TIMEOUT = 1 /* nlls_iter_end_peer: a peer's stamp did not arrive within the timeout */ };
+
 enum { NLLS_SOLVER_GN = 0, NLLS_SOLVER_LM = 1, NLLS_SOLVER_GD = 2 };
 enum { NLLS_LM_LEVENBERG = 0, NLLS_LM_MARQUARDT = 1 };
 enum { NLLS_MODEL_EMG = 0, NLLS_MODEL_SKEWGAUSS = 1,
@@ -58,7 +60,7 @@ typedef struct nlls_ctrl {
   int done;          /* 1 once every problem of the batch satisfied a stop test (lma:118, gna:88, gda:84) */
   int iters;         /* iterations completed == snapshots written to p_hist */
   int singular;      /* sticky: some solve met a non-positive / non-finite pivot (gna:74-75 warning) */
-  int reserved;
+  int error;         /* sticky: NLLS_CTRL_E_* set by a kernel (0 = none); done is set with it */
   double red[4];
 } nlls_ctrl;
 
@@ -139,10 +141,12 @@ int nlls_iter_end(nlls_ctrl* ctrl, int solver, double ftol, void* stream);
 /* nlls_iter_end for a batch sharded over the GPUs of one box in "exact" mode (lma:110,118, gna:88, gda:76,84 see the
  * WHOLE batch): sums ctrl->red over the ranks through peer-mapped mailboxes (NVLink P2P stores + stamp, no collective
  * library call) and then decides like nlls_iter_end.  mailboxes: device array of `world` pointers, entry r = rank r's
- * mailbox of 2*world*8 doubles (zero-initialised symmetric memory, mapped into this process); epoch: a per-solve
- * counter, equal on every rank.  Every rank has to launch it once per iteration. */
+ * mailbox of 4*world*8 doubles (zero-initialised symmetric memory, mapped into this process; slot = 2*(epoch&1) +
+ * (iteration&1)); epoch: a per-solve counter, equal on every rank.  Every rank has to launch it once per iteration.
+ * A peer that stays silent for timeout_s seconds (<= 0: 60 s) sets ctrl->error = NLLS_CTRL_E_PEER_TIMEOUT and
+ * ctrl->done = 1 on the waiting rank (no trap: its context and earlier results survive). */
 int nlls_iter_end_peer(nlls_ctrl* ctrl, int solver, double ftol, void* const* mailboxes, int rank, int world,
-                       long long epoch, void* stream);
+                       long long epoch, double timeout_s, void* stream);
 
 /* ---- single-problem solvers (torchimize/functions/single/*.py: lma_fun_single.py:81,99; gna:81; gda:78) ----------
  * Residual statistics of ONE problem over a vector of any length, spread over the whole GPU: block k writes

@@ -89,7 +89,8 @@ def case_cfg2(kind, dtname='f64'):
     w = torch.ones(C, dtype=dt, device=DEV)
     kw = dict(meth='lev') if kind == 'lm' else {}
     ms, iters, kern = timed_solve(SOLVERS[kind], p0, EMGModel(), (t, y), w, 40 if kind == 'lm' else 80, **kw)
-    bytes_of = {'nlls_model_normal_eq': 3 * s * C * N * B, 'nlls_model_lm_trial': 3 * s * C * N * B, 'nlls_model_cost_stat': s * C * N * B,
+    # DRAM traffic the kernels are designed to move: y once, m_prev read + m written ([B,N] each)
+    bytes_of = {'nlls_model_normal_eq': s * N * (C + 2) * B, 'nlls_model_lm_trial': s * N * (C + 2) * B, 'nlls_model_cost_stat': s * C * N * B,
                 'nlls_model_normal_eq_gda': (s * C * N + 2 * s * N) * B}
     report(f'cfg2-{kind}' + ('' if dtname == 'f64' else '-f32'), B, ms, iters, kern, bytes_of)
 
@@ -101,7 +102,8 @@ def case_cfg3(kind, P=5):
     w = torch.ones(C, dtype=dt, device=DEV)
     kw = dict(meth='lev') if kind == 'lm' else {}
     ms, iters, kern = timed_solve(SOLVERS[kind], p0, SkewGaussModel(), (x, y), w, 40 if kind == 'lm' else 80, **kw)
-    bytes_of = {'nlls_model_normal_eq': 3 * s * C * N * B, 'nlls_model_lm_trial': 3 * s * C * N * B, 'nlls_model_cost_stat': s * C * N * B,
+    # DRAM traffic the kernels are designed to move: y once, m_prev read + m written ([B,N] each)
+    bytes_of = {'nlls_model_normal_eq': s * N * (C + 2) * B, 'nlls_model_lm_trial': s * N * (C + 2) * B, 'nlls_model_cost_stat': s * C * N * B,
                 'nlls_model_normal_eq_gda': (s * C * N + 2 * s * N) * B}
     report(f'cfg3-{kind}-P{P}', B, ms, iters, kern, bytes_of)
 

@@ -7,7 +7,7 @@ for l in open(sys.argv[1] if len(sys.argv) > 1 else 'gpurun_out/configs.log'):
         print(l[:300].rstrip())
         continue
     d = json.loads(l)
-    if 'error' in d:
+    if 'error' in d or 'variant' in d:
         print(d)
         continue
     print(d['case'], 'B', d['B'], 'ms/solve', round(d.get('ms_per_solve', 0), 2), 'iters', d.get('iterations'), 'prob/s',

@@ -37,7 +37,7 @@ def _report_boundary_flips():
         return
     kind = 'gpu' if torch.cuda.is_available() else 'cpu'
     rec = {'what': 'fp32 iteration-count flips against the reference golden trajectories (tests/helpers.py::compare_plist, '
-                   f'bound +-{helpers.MAX_FLIP}); ours = ' + ('CUDA path' if kind == 'gpu' else 'CPU oracle'),
+                   'bound: 1 iteration or the measured spread of the reference algorithm\'s own fp32 count, tests/golden/fp32_count_spread.json); ours = ' + ('CUDA path' if kind == 'gpu' else 'CPU oracle'),
            'comparisons': len(helpers.COMPARED), 'flips': helpers.FLIPS, 'compared': helpers.COMPARED}
     for d in ('profiles', 'gpurun_out'):
         path = os.path.join(ROOT, d)

@@ -35,7 +35,7 @@ def test_abi_version_and_ctrl_size():
 
     class Ctrl(ctypes.Structure):
         _fields_ = [('done', ctypes.c_int), ('iters', ctypes.c_int), ('singular', ctypes.c_int),
-                    ('reserved', ctypes.c_int), ('red', ctypes.c_double * 4)]
+                    ('error', ctypes.c_int), ('red', ctypes.c_double * 4)]
     assert ctypes.sizeof(Ctrl) == _lib.CTRL_BYTES
 
 

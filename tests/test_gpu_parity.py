@@ -239,7 +239,7 @@ def _torch_emg(n_costs):
     return (lambda p, t, y: M.emg_cost(p, t, y, n_costs=n_costs)), (lambda p, t, y: M.emg_jac(p, t, y, n_costs=n_costs))
 
 
-def _solve_case(gold, name, dn, fun, jac, args, prefix='', chaotic=False, **extra):
+def _solve_case(gold, name, dn, fun, jac, args, prefix='', chaotic=False, gset='', **extra):
     key = f'{prefix}{name}__{dn}'
     if key + '__raises' in gold:
         pytest.skip('reference raises on this input (Marquardt overflow, Q6)')
@@ -251,7 +251,7 @@ def _solve_case(gold, name, dn, fun, jac, args, prefix='', chaotic=False, **extr
     assert torch.equal(pl[-1], p), 'caller p must end as the final iterate (Q1)'
     if chaotic:
         return compare_chaotic(pl, gold[key + '__plist'], dn, key)
-    return compare_plist(pl, gold[key + '__plist'], dn, key, allow_boundary=(dn == 'f32'))
+    return compare_plist(pl, gold[key + '__plist'], dn, gset + key, allow_boundary=(dn == 'f32'), spread_key=gset + key)
 
 
 PATHS = ['torch_callables', 'cuda_callables', 'fused']
@@ -283,7 +283,7 @@ def test_synthetic_cases_match_reference(name, dn, path):
     gold = load('synthetic')
     dt = DT[dn]
     fun, jac, extra = _emg_path(path, None)
-    _solve_case(gold, name, dn, fun, jac, (cu(gold['t'], dt), cu(gold['y'], dt)), chaotic=name in CHAOTIC['synthetic'], **extra)
+    _solve_case(gold, name, dn, fun, jac, (cu(gold['t'], dt), cu(gold['y'], dt)), chaotic=name in CHAOTIC['synthetic'], gset='synthetic:', **extra)
 
 
 @pytest.mark.parametrize('path', PATHS)

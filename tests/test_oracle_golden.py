@@ -34,7 +34,7 @@ def skew():
     return load('skewgauss')
 
 
-def _run_case(gold, name, dn, fun, jac, args, prefix=''):
+def _run_case(gold, name, dn, fun, jac, args, prefix='', gset=''):
     key = f'{prefix}{name}__{dn}'
     dt = DT[dn]
     solver, kw = CASES[name]
@@ -44,7 +44,7 @@ def _run_case(gold, name, dn, fun, jac, args, prefix=''):
         pytest.skip('reference raises on this input (Marquardt overflow, Q6)')
     tr = getattr(O, solver)(p, fun, jac, args=args, wvec=w, **kw)
     assert torch.equal(tr.p_list[-1], p), 'oracle must mutate p in place like the reference (Q1)'
-    return compare_plist(tr.p_list, gold[key + '__plist'], dn, key, allow_boundary=(dn == 'f32'))
+    return compare_plist(tr.p_list, gold[key + '__plist'], dn, gset + key, allow_boundary=(dn == 'f32'), spread_key=gset + key)
 
 
 @pytest.mark.parametrize('dn', ['f64', 'f32'])
@@ -58,7 +58,7 @@ def test_fixture_cases(fixtures, name, dn):
 @pytest.mark.parametrize('name', list(CASES))
 def test_synthetic_cases(synthetic, name, dn):
     fun, jac, args = _emg_args(synthetic, DT[dn])
-    _run_case(synthetic, name, dn, fun, jac, args)
+    _run_case(synthetic, name, dn, fun, jac, args, gset='synthetic:')
 
 
 @pytest.mark.parametrize('dn', ['f64', 'f32'])
@@ -81,7 +81,7 @@ def test_cfg5_shape_cases(name, dn):
     solver, kw = CASES5[name]
     p = torch.as_tensor(gold['p0']).to(dt).clone()
     tr = getattr(O, solver)(p, fun, jac, args=args, wvec=torch.as_tensor(gold['wvec']).to(dt), **kw)
-    compare_plist(tr.p_list, gold[f'{name}__{dn}__plist'], dn, f'cfg5 {name}__{dn}', allow_boundary=(dn == 'f32'))
+    compare_plist(tr.p_list, gold[f'{name}__{dn}__plist'], dn, f'cfg5 {name}__{dn}', allow_boundary=(dn == 'f32'), spread_key=f'cfg5 {name}__{dn}')
 
 
 @pytest.mark.parametrize('dn', ['f64', 'f32'])

@@ -182,7 +182,8 @@ def _w_exact_gpu(rank, world, name, dn, path):
         _engine.set_default_reduce_hook(old)
     want = torch.as_tensor(gold[f'{name}__{dn}__plist'])
     lo, hi = sharding.shard_bounds(want.shape[1], world, rank)
-    Hh.compare_plist(got, want[:, lo:hi], dn, f'exact-sharded {name} {dn} {path} rank {rank}', allow_boundary=(dn == 'f32'))
+    Hh.compare_plist(got, want[:, lo:hi], dn, f'exact-sharded {name} {dn} {path} rank {rank}', allow_boundary=(dn == 'f32'),
+                     spread_key=f'{name}__{dn}')
 
 
 @pytest.mark.gpu

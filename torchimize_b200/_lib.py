@@ -1,6 +1,7 @@
 """ctypes binding of libnlls_b200.so (C ABI: include/nlls_b200.h).  Plumbing only: torch owns
 device memory and streams, the library owns every kernel."""
 import ctypes
+import functools
 import os
 import subprocess
 import threading
@@ -16,6 +17,7 @@ SOLVER_GN, SOLVER_LM, SOLVER_GD = 0, 1, 2
 LM_LEVENBERG, LM_MARQUARDT = 0, 1
 MODEL_EMG, MODEL_SKEWGAUSS, MODEL_MULTI_EMG, MODEL_USER = 0, 1, 2, 100
 CTRL_BYTES = 48
+CTRL_E_PEER_TIMEOUT = 1
 
 _vp, _i, _ll, _d = ctypes.c_void_p, ctypes.c_int, ctypes.c_longlong, ctypes.c_double
 
@@ -32,7 +34,7 @@ SIGNATURES = {
     'nlls_gn_update': [_i, _vp, _vp, _vp, _vp, _d, _d, _d, _d, _i, _ll, _i, _vp, _vp, _vp, _vp],
     'nlls_gd_update': [_i, _vp, _vp, _vp, _vp, _d, _d, _d, _d, _i, _ll, _i, _vp, _vp, _vp, _vp],
     'nlls_iter_end': [_vp, _i, _d, _vp],
-    'nlls_iter_end_peer': [_vp, _i, _d, _vp, _i, _i, _ll, _vp],
+    'nlls_iter_end_peer': [_vp, _i, _d, _vp, _i, _i, _ll, _d, _vp],
     'nlls_sumsq_partials': [],
     'nlls_sumsq': [_i, _vp, _vp, _ll, _vp, _vp],
     'nlls_model_eval': [_i, _i, _vp, _i, _vp, _vp, _ll, _ll, _ll, _i, _i, _vp, _vp, _vp, _vp],
@@ -174,6 +176,22 @@ def require_cuda(*tensors):
 
 def stream_ptr():
     return torch.cuda.current_stream().cuda_stream
+
+
+def on_device_of(argpos, name='p'):
+    """Decorator: run the function with the CUDA device of its tensor argument (position `argpos` or keyword `name`)
+    made current.  The library launches on the CURRENT device's stream and sizes its grids from the current device;
+    the reference accepts tensors on any device, so a solve of a cuda:1 tensor while cuda:0 is current has to switch."""
+    def deco(fn):
+        @functools.wraps(fn)
+        def wrapped(*a, **kw):
+            t = a[argpos] if len(a) > argpos else kw.get(name)
+            if torch.is_tensor(t) and t.is_cuda and t.device.index != torch.cuda.current_device():
+                with torch.cuda.device(t.device):
+                    return fn(*a, **kw)
+            return fn(*a, **kw)
+        return wrapped
+    return deco
 
 
 _timing = None        # when a list: (name, start_event, end_event) per call (bench.py's per-kernel breakdown)

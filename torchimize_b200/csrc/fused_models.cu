@@ -234,16 +234,20 @@ struct TileRing {
 // or occupancy.  TN = TPB * S samples per tile.  One __syncthreads per tile (stage hand-back) and
 // one per problem (cross-warp sums, double-buffered); the per-problem warp sums use the
 // transposed reduction (16 shuffles for P = 4 instead of 80).
-template <typename T, typename Model, int TPB, int S, int NSTAGE>
-__global__ void __launch_bounds__(TPB)
+// CT > 0: the number of costs is a compile-time constant (dispatch: C <= 8): the cost loop is fully unrolled, the cost
+// weights and the per-cost sums of f live in registers (no shared-memory read-modify-write per cost and tile) and the
+// C * S residual chains of a tile are independent instruction streams for the scheduler.  CT == 0: any C at run time.
+template <typename T, typename Model, int TPB, int S, int NSTAGE, int CT = 0, int MINB = 0>
+__global__ void __launch_bounds__(TPB, MINB > 0 ? MINB : 512 / TPB)
 k_model_normal_eq_staged(const T* __restrict__ p, const T* __restrict__ x, const T* __restrict__ y, long long ybs,
-                         long long ycs, const T* __restrict__ w, int wlen, long long B, int C, int N, T* mA, T* mB,
+                         long long ycs, const T* __restrict__ w, int wlen, long long B, int C_, int N, T* mA, T* mB,
                          T* __restrict__ g, T* __restrict__ H, double* __restrict__ stats, const nlls_ctrl* ctrl,
                          const unsigned char* __restrict__ sel) {
   if (is_done(ctrl)) return;
   constexpr int P = Model::P, NW = TPB / 32, NH = Tri<P>::N, V = P + NH + 2, TN = TPB * S;
   constexpr int VP = Pow2Ceil<V>::value, OWN = 32 / VP;      // transposed reduction: lane L owns value L / OWN
   static_assert(V <= 32, "model with too many parameters for the transposed reduction");
+  const int C = CT > 0 ? CT : C_;
   const int it = iter_index(ctrl);
   T* m_out = (it & 1) ? mB : mA;
   const T* m_prev = (it > 0 && mA) ? ((it & 1) ? mA : mB) : nullptr;
@@ -303,44 +307,50 @@ k_model_normal_eq_staged(const T* __restrict__ p, const T* __restrict__ x, const
     acc.clear();
     double sd = 0.0, sq = 0.0;
     double* my_sfc = sfc + (size_t)pbuf * C * TPB + tid;
-    for (int c = 0; c < C; ++c) my_sfc[c * TPB] = 0.0;
+    [[maybe_unused]] double sfr[CT > 0 ? CT : 1];             // CT: per-cost sums of f in registers
+    if constexpr (CT > 0) {
+#pragma unroll
+      for (int c = 0; c < CT; ++c) sfr[c] = 0.0;
+    } else {
+      for (int c = 0; c < C; ++c) my_sfc[c * TPB] = 0.0;
+    }
     if (sel) m_out = sel[b] ? mA : mB;
     T* mo_b = m_out ? m_out + b * (long long)N : nullptr;
-    for (int n0 = 0; n0 < N; n0 += TN) {
-      T m[S], k[S][P], s2[S], s3[S];
+    // FULL tiles (n0 + TN <= N) carry no per-sample bounds predicates: the tile body is one straight-line block in which
+    // the S model evaluations and the C * S residual chains interleave.
+    auto tile = [&](int n0, auto full_tag) {
+      constexpr bool FULL = decltype(full_tag)::value;
+      T xv[S], m[S], k[S][P], s2[S], s3[S];
 #pragma unroll
       for (int i = 0; i < S; ++i) {
         const int n = n0 + i * TPB + tid;
-        M.eval(ld_cached(x + min(n, N - 1)), m[i], k[i]);    // overlaps the wait below
+        xv[i] = ld_cached(x + (FULL ? n : min(n, N - 1)));
         s2[i] = T(0);
         s3[i] = T(0);
       }
+      model_eval_n<Model, T, S>(M, xv, m, k);               // overlaps the wait below
       if (mo_b) {
 #pragma unroll
         for (int i = 0; i < S; ++i)
-          if (n0 + i * TPB + tid < N) stg_stream(mo_b + n0 + i * TPB + tid, m[i]);
+          if (FULL || n0 + i * TPB + tid < N) stg_stream(mo_b + n0 + i * TPB + tid, m[i]);
       }
       mbar_wait(&bars[st], ph);
       const T* yc = ring + (size_t)st * stage_elems + tid;
       const int ystep = (Cy == 1) ? 0 : TN;
-      T mp[S];
+      T mp[S];                                               // without a previous iterate: m itself (f_prev - f == 0 exactly)
 #pragma unroll
-      for (int i = 0; i < S; ++i) mp[i] = has_prev ? yc[Cy * TN + i * TPB] : T(0);   // rows past N: stale, masked below
-#pragma unroll 2
-      for (int c = 0; c < C; ++c, yc += ystep) {
-        const T wc = w[wlen == 1 ? 0 : c];
+      for (int i = 0; i < S; ++i) mp[i] = has_prev ? yc[Cy * TN + i * TPB] : m[i];   // rows past N: stale, masked below
+      auto cost = [&](const T* yrow, T wc) -> double {        // one cost of this tile; returns the thread's sum of f
         double sfl = 0.0;
 #pragma unroll
         for (int i = 0; i < S; ++i) {
-          if (n0 + i * TPB + tid < N) {
-            const T yv = yc[i * TPB];
+          if (FULL || n0 + i * TPB + tid < N) {
+            const T yv = yrow[i * TPB];
             const T r = yv - m[i];
             const T fv = mul_rn(r, r);
-            if (has_prev) {                                  // f_prev rebuilt from the stored model value (bit-identical)
-              const T rp = yv - mp[i];
-              const T d = mul_rn(rp, rp) - fv;
-              sd = fma((double)d, (double)d, sd);
-            }
+            const T rp = yv - mp[i];                         // f_prev rebuilt from the stored model value (bit-identical)
+            const T d = mul_rn(rp, rp) - fv;
+            sd = fma((double)d, (double)d, sd);
             sq = fma((double)fv, (double)fv, sq);
             sfl += (double)fv;
             const T wf = wc * fv;
@@ -348,16 +358,31 @@ k_model_normal_eq_staged(const T* __restrict__ p, const T* __restrict__ x, const
             s3[i] = fma(wf, r, s3[i]);
           }
         }
-        my_sfc[c * TPB] += sfl;
+        return sfl;
+      };
+      if constexpr (CT > 0) {
+#pragma unroll
+        for (int c = 0; c < CT; ++c) sfr[c] += cost(yc + c * ystep, w[wlen == 1 ? 0 : c]);
+      } else {
+#pragma unroll 2
+        for (int c = 0; c < C; ++c, yc += ystep) my_sfc[c * TPB] += cost(yc, w[wlen == 1 ? 0 : c]);
       }
 #pragma unroll
       for (int i = 0; i < S; ++i)
-        if (n0 + i * TPB + tid < N) acc.add_scaled(k[i], T(2) * s3[i], T(4) * s2[i]);
+        if (FULL || n0 + i * TPB + tid < N) acc.add_scaled(k[i], T(2) * s3[i], T(4) * s2[i]);
+    };
+    for (int n0 = 0; n0 < N; n0 += TN) {
+      if (n0 + TN <= N) tile(n0, std::true_type{});
+      else tile(n0, std::false_type{});
       if (n0 + TN < N) {
         __syncthreads();                                     // every thread is done with this stage
         if (tid == 0) issue();
       }
       if (++st == NSTAGE) { st = 0; ph ^= 1u; }
+    }
+    if constexpr (CT > 0) {
+#pragma unroll
+      for (int c = 0; c < CT; ++c) my_sfc[c * TPB] = sfr[c];
     }
     // ---- per-problem sums: transposed warp reduction, then fp64 across warps through smem
     double v[VP];
@@ -1189,10 +1214,12 @@ k_model_normal_eq_gda_staged(const T* __restrict__ p, const T* __restrict__ x, c
     RowAcc<double, P> acc;
     acc.clear();
     double sd = 0.0, sq = 0.0;
-    for (int n0 = 0; n0 < N; n0 += TN) {
-      T m[S], k[S][P];
+    auto tile = [&](int n0, auto full_tag) {                 // FULL tiles: no per-sample bounds predicates (straight-line body)
+      constexpr bool FULL = decltype(full_tag)::value;
+      T xv[S], m[S], k[S][P];
 #pragma unroll
-      for (int i = 0; i < S; ++i) M.eval(ld_cached(x + min(n0 + i * TPB + tid, N - 1)), m[i], k[i]);
+      for (int i = 0; i < S; ++i) xv[i] = ld_cached(x + (FULL ? n0 + i * TPB + tid : min(n0 + i * TPB + tid, N - 1)));
+      model_eval_n<Model, T, S>(M, xv, m, k);
       const T* sy = R.wait() + tid;
       const T* sp = sy + Cy * TN;
       const int ystep = (Cy == 1) ? 0 : TN;
@@ -1212,16 +1239,21 @@ k_model_normal_eq_gda_staged(const T* __restrict__ p, const T* __restrict__ x, c
 #pragma unroll
       for (int i = 0; i < S; ++i) {
         const int n = n0 + i * TPB + tid;
-        if (n < N) {
+        if (FULL || n < N) {
           double jd[P];
 #pragma unroll
           for (int q = 0; q < P; ++q) jd[q] = (double)(T(2) * s1[i] * k[i][q]);   // gda:137 (cost-summed row, in T)
           acc.add(jd, (double)fs[i], 1.0);
           if (fs_out) fs_out[b * N + n] = fs[i];
           sq = fma((double)fs[i], (double)fs[i], sq);
-          if (has_prev) { const T d = sp[i * TPB] - fs[i]; sd = fma((double)d, (double)d, sd); }
+          const T d = (has_prev ? sp[i * TPB] : fs[i]) - fs[i];   // no previous iterate: 0 exactly
+          sd = fma((double)d, (double)d, sd);
         }
       }
+    };
+    for (int n0 = 0; n0 < N; n0 += TN) {
+      if (n0 + TN <= N) tile(n0, std::true_type{});
+      else tile(n0, std::false_type{});
       if (n0 + TN < N) {
         __syncthreads();
         if (tid == 0) R.issue();
@@ -1531,7 +1563,7 @@ static int fused_variant() {
 template <typename T> static bool vec_family() { return sizeof(T) == 4 && fused_variant() == 0; }
 
 // returns 0 when launched, 1 when the shape is not eligible for bulk copies, or a launch error
-template <typename T, typename Model, int TPB2, int S2>
+template <typename T, typename Model, int TPB2, int S2, int CT = 0, int MINB = 0>
 static int launch_staged(const ModelArgs& a) {
   constexpr int P = Model::P, V = P + Tri<P>::N + 2, NW2 = TPB2 / 32, TN = TPB2 * S2, VP = Pow2Ceil<V>::value;
   const size_t es = sizeof(T);
@@ -1541,8 +1573,9 @@ static int launch_staged(const ModelArgs& a) {
   const bool ok16 = aligned_to(a.y, 16) && (a.ybs * es) % 16 == 0 && (a.ycs * es) % 16 == 0 && ((size_t)a.N * es) % 16 == 0 &&
                     (!a.fA || (aligned_to(a.fA, 16) && aligned_to(a.fB, 16)));
   if (!ok16) return 1;
+  if (CT > 0 && a.C != CT) return 1;
   // as many CTAs per SM as registers allow (64K regs / (128 regs x TPB2)); 3 stages if they still fit, else 2
-  const int want_ctas = 512 / TPB2;
+  const int want_ctas = MINB > 0 ? MINB : 512 / TPB2;
   const bool three = (size_t)want_ctas * (3 * stage + tail + 1024) <= 226 * 1024;
   const size_t smem2 = (three ? 3 : 2) * stage + tail;
   if (smem2 > 220 * 1024) return 1;
@@ -1551,11 +1584,32 @@ static int launch_staged(const ModelArgs& a) {
     kern2<<<grid2, TPB2, smem2, a.st>>>((const T*)a.p, (const T*)a.x, (const T*)a.y, a.ybs, a.ycs, (const T*)a.w, a.wlen,
                                         a.B, a.C, a.N, (T*)a.fA, (T*)a.fB, (T*)a.g, (T*)a.H, a.stats, a.ctrl, a.sel);
   };
-  if (three) launch(k_model_normal_eq_staged<T, Model, TPB2, S2, 3>);
-  else launch(k_model_normal_eq_staged<T, Model, TPB2, S2, 2>);
+  if (three) launch(k_model_normal_eq_staged<T, Model, TPB2, S2, 3, CT, MINB>);
+  else launch(k_model_normal_eq_staged<T, Model, TPB2, S2, 2, CT, MINB>);
   return check_launch("nlls_model_normal_eq(staged)");
 }
 
+
+// fp64 default: up to 8 costs as a compile-time constant, 64-thread CTAs with 4 samples per thread, 6 CTAs per SM (166
+// registers, no spills): 20 independent residual chains per thread and tile.  cfg-2 GN fp64 on one box (profiles/r02e):
+// run-time C at 128 x 2: 1.065 ms; compile-time C at 128 x 2 (128 registers): 0.998 ms; at 64 x 4: 0.929 ms.
+template <typename T, typename Model>
+static int launch_staged_ct(const ModelArgs& a) {
+  if constexpr (sizeof(T) == 8) {
+    switch (a.C) {
+      case 1: return launch_staged<T, Model, 64, 4, 1, 6>(a);
+      case 2: return launch_staged<T, Model, 64, 4, 2, 6>(a);
+      case 3: return launch_staged<T, Model, 64, 4, 3, 6>(a);
+      case 4: return launch_staged<T, Model, 64, 4, 4, 6>(a);
+      case 5: return launch_staged<T, Model, 64, 4, 5, 6>(a);
+      case 6: return launch_staged<T, Model, 64, 4, 6, 6>(a);
+      case 7: return launch_staged<T, Model, 64, 4, 7, 6>(a);
+      case 8: return launch_staged<T, Model, 64, 4, 8, 6>(a);
+      default: break;
+    }
+  }
+  return launch_staged<T, Model, 128, 2>(a);
+}
 
 // 128-bit-lane staged kernel: same eligibility as launch_staged plus a 16-byte aligned abscissa
 template <typename T, typename Model, int TPB2>
@@ -1721,16 +1775,18 @@ static int run_op(Op op, const ModelArgs& a) {
 #ifndef NLLS_USER_MODEL_HEADER                               // tuning variants: built-in models only (plugin compile time)
           case 1: rc = launch_staged<T, Model, 256, 2>(a); break;
           case 2: rc = launch_staged<T, Model, 64, 2>(a); break;
-          case 3: rc = launch_staged<T, Model, 64, 4>(a); break;
           case 5: rc = launch_vec<T, Model, 128>(a); break;
           case 6: rc = launch_vec<T, Model, 64>(a); break;
           case 7: rc = launch_vec<T, Model, 256>(a); break;
+          case 8: rc = launch_staged<T, Model, 128, 2, 5, 4>(a); break;       // compile-time C = 5 at other CTA shapes
+          case 10: rc = launch_staged<T, Model, 128, 2, 5, 3>(a); break;
+          case 11: rc = launch_staged<T, Model, 128, 2, 0, 0>(a); break;      // run-time C (the C > 8 kernel)
 #endif
           default:
             // fp32: 128-bit lanes, 64-thread CTAs (cfg-2 fp32 1.01 -> 0.76 ms, profiles/r01f); fp64 is HBM-bound either
             // way and measures a little better with the strided map at 4 CTAs/SM (r01 sweeps)
             if (vec_family<T>()) rc = launch_vec<T, Model, 64>(a);
-            if (rc == 1) rc = launch_staged<T, Model, 128, 2>(a);
+            if (rc == 1) rc = launch_staged_ct<T, Model>(a);
             break;
         }
         if (rc <= 0) return rc;                              // 0 launched, < 0 error, 1 = shape not eligible
@@ -1772,6 +1828,9 @@ static int run_op(Op op, const ModelArgs& a) {
         else
 #endif
         if (vec_family<T>()) rc = launch_cost_vec<T, Model, 64>(a);
+        // same sample-to-thread map as the normal-equation kernel of the same shape (launch_staged_ct): the two-pass and
+        // the speculative LM schedules see the same bits in stats[0]
+        if (rc == 1 && sizeof(T) == 8 && a.C <= 8) rc = launch_cost_staged<T, Model, 64, 4>(a);
         if (rc == 1) rc = launch_cost_staged<T, Model, 128, 2>(a);
         if (rc <= 0) return rc;
       }

@@ -41,8 +41,9 @@ template <typename T> struct ExpNeg;
 __constant__ double kExpTaylor[12] = {1.6059043836821613e-10, 2.08767569878681e-09, 2.505210838544172e-08, 2.755731922398589e-07,
                                       2.7557319223985893e-06, 2.48015873015873e-05, 0.0001984126984126984, 0.001388888888888889,
                                       0.008333333333333333, 0.041666666666666664, 0.16666666666666666, 0.5};
+// Branch-free (the flush and the NaN case are selects at the end): several calls in one basic block — the two exps of a
+// sample, the samples of a thread — interleave their 14-deep Horner chains instead of running one after the other.
 __device__ __forceinline__ double exp_nonpos(double x) {
-  if (x < -707.0) return 0.0;
   const double magic = 6755399441055744.0;                   // 1.5 * 2^52: fma rounds x*log2(e) to the nearest integer
   double t = fma(x, 1.4426950408889634, magic);
   const int n = __double2loint(t);
@@ -54,7 +55,8 @@ __device__ __forceinline__ double exp_nonpos(double x) {
   for (int i = 1; i < 12; ++i) q = fma(q, r, kExpTaylor[i]);
   q = fma(q, r, 1.0);
   q = fma(q, r, 1.0);
-  return __hiloint2double(__double2hiint(q) + (n << 20), __double2loint(q));
+  const double e = __hiloint2double(__double2hiint(q) + (n << 20), __double2loint(q));
+  return x >= -707.0 ? e : (x < -707.0 ? 0.0 : x);          // flushed tail; NaN propagates
 }
 template <> struct ExpNeg<double> {
   static __device__ __forceinline__ double prep(double c) { return c; }
@@ -124,12 +126,16 @@ struct EmgModel {
     const T A = one_plus_erf<T>(x, E);                        // asymm_term, emg.py:21
     return alpha * (G * A);                                   // same association as eval(): bit-identical m
   }
-  __device__ __forceinline__ void eval(T t, T& m, T (&k)[P]) const {
-    const T d = t - mu;
-    const T G = ExpNeg<T>::eval(d * d, inv_s2h);
-    const T x = xs * d;
-    const T E = ExpNeg<T>::sq(x);                           // erf_term, emg.py:26
-    const T A = one_plus_erf<T>(x, E);
+  // eval() in three phases, so that callers with several evaluations in flight (the samples of a thread, the peaks of a
+  // multi-peak model) can run every phase-1 first: (1) both exps, branch-free — their dependent chains interleave;
+  // (2) the erf term (fp64: early-out branch); (3) the product rule.
+  __device__ __forceinline__ void phase1(T t, T& d, T& G, T& x, T& E) const {
+    d = t - mu;
+    G = ExpNeg<T>::eval(d * d, inv_s2h);                      // gauss_term, emg.py:20
+    x = xs * d;
+    E = ExpNeg<T>::sq(x);                                     // erf_term, emg.py:26
+  }
+  __device__ __forceinline__ void phase3(T d, T G, T E, T A, T& m, T* k) const {
     const T q = d * inv_s;
     const T GA = G * A;
     m = alpha * GA;
@@ -140,7 +146,40 @@ struct EmgModel {
     k[2] = k[1] * q;
     k[3] = -aG * T(0.7978845608028654) * q * E;               // emg.py:45-46
   }
+  __device__ __forceinline__ void eval(T t, T& m, T (&k)[P]) const {
+    T d, G, x, E;
+    phase1(t, d, G, x, E);
+    const T A = one_plus_erf<T>(x, E);                        // asymm_term, emg.py:21
+    phase3(d, G, E, A, m, k);
+  }
+  template <int S>
+  __device__ __forceinline__ void eval_n(const T (&t)[S], T (&m)[S], T (&k)[S][P]) const {
+    T d[S], G[S], x[S], E[S], A[S];
+#pragma unroll
+    for (int i = 0; i < S; ++i) phase1(t[i], d[i], G[i], x[i], E[i]);
+#pragma unroll
+    for (int i = 0; i < S; ++i) A[i] = one_plus_erf<T>(x[i], E[i]);
+#pragma unroll
+    for (int i = 0; i < S; ++i) phase3(d[i], G[i], E[i], A[i], m[i], k[i]);
+  }
 };
+
+// model_eval_n: a model's own eval_n when it has one, otherwise eval() sample by sample (user functors need only eval()).
+template <typename Model, typename T, int S, typename = void>
+struct EvalN {
+  static __device__ __forceinline__ void run(const Model& M, const T (&t)[S], T (&m)[S], T (&k)[S][Model::P]) {
+#pragma unroll
+    for (int i = 0; i < S; ++i) M.eval(t[i], m[i], k[i]);
+  }
+};
+template <typename Model, typename T, int S>
+struct EvalN<Model, T, S, decltype((void)&Model::template eval_n<S>)> {
+  static __device__ __forceinline__ void run(const Model& M, const T (&t)[S], T (&m)[S], T (&k)[S][Model::P]) { M.template eval_n<S>(t, m, k); }
+};
+template <typename Model, typename T, int S>
+__device__ __forceinline__ void model_eval_n(const Model& M, const T (&t)[S], T (&m)[S], T (&k)[S][Model::P]) {
+  EvalN<Model, T, S>::run(M, t, m, k);
+}
 
 // Sum of K EMG peaks, p = [alpha_1, mu_1, sigma_1, eta_1, ..., alpha_K, mu_K, sigma_K, eta_K] (the
 // large-P workload of cfg-4, 4 peaks = 16 parameters).  Values are summed in peak order; the derivative block of peak
@@ -159,14 +198,17 @@ struct MultiEmgModel {
     for (int j = 1; j < K; ++j) m += peak[j].value(t);
     return m;
   }
-  __device__ __forceinline__ void eval(T t, T& m, T (&k)[P]) const {
+  __device__ __forceinline__ void eval(T t, T& m, T (&k)[P]) const {         // the K peaks in EmgModel's three phases
+    T d[K], G[K], x[K], E[K], A[K];
+#pragma unroll
+    for (int j = 0; j < K; ++j) peak[j].phase1(t, d[j], G[j], x[j], E[j]);
+#pragma unroll
+    for (int j = 0; j < K; ++j) A[j] = one_plus_erf<T>(x[j], E[j]);
 #pragma unroll
     for (int j = 0; j < K; ++j) {
-      T mj, kj[4];
-      peak[j].eval(t, mj, kj);
+      T mj;
+      peak[j].phase3(d[j], G[j], E[j], A[j], mj, k + 4 * j);
       m = j == 0 ? mj : m + mj;
-#pragma unroll
-      for (int i = 0; i < 4; ++i) k[4 * j + i] = kj[i];
     }
   }
 };

@@ -372,34 +372,56 @@ __global__ void k_iter_end(nlls_ctrl* ctrl, int solver, double ftol) {
 
 // Multi-GPU "exact" mode without a collective library call: the batch-global stop test needs the SUM over the ranks of
 // the four fp64 reductions of ONE iteration (32 bytes).  Every rank owns a mailbox in peer-mapped (symmetric) memory,
-// [2 parities][world][8 doubles]; thread t of this one-block kernel stores this rank's sums and then a stamp straight into
+// [4 slots][world][8 doubles]; thread t of this one-block kernel stores this rank's sums and then a stamp straight into
 // rank t's mailbox over NVLink (P2P stores, data -> __threadfence_system -> stamp), then spins on the stamp of rank t in
 // its OWN mailbox, reads that rank's sums, and thread 0 adds them in rank order (identical bits on every rank) before the
-// usual decision.  Slots alternate with the iteration parity: a rank can run at most one iteration ahead of a peer,
-// because it needs that peer's stamp of the previous iteration to get there.  The stamp carries a per-solve epoch so
-// that a slot left over from an earlier solve can never match.  A peer that does not answer within ~2 s traps.
+// usual decision.  slot = 2 * (epoch & 1) + (iteration & 1): a rank can run at most one iteration ahead of a peer (it
+// needs that peer's stamp of the previous iteration to get there), and at most one SOLVE ahead (its first iteration of
+// solve e+1 needs the peer's stamp of that iteration, which the peer's stream posts only after it finished solve e), so
+// neither consecutive iterations nor consecutive solves ever share a slot.  The stamp carries the per-solve epoch so
+// that a slot left over from an earlier solve can never match.  A peer that does not answer within timeout_ns sets the
+// sticky ctrl->error and ctrl->done (every later kernel of the solve returns at once; the host raises after its flag
+// read) instead of trapping: a trap would destroy the context and every result of the rank that waited.
+__device__ __forceinline__ unsigned long long global_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+
 __global__ void k_iter_end_peer(nlls_ctrl* ctrl, int solver, double ftol, double* const* __restrict__ mbox, int rank, int world,
-                                long long epoch) {
+                                long long epoch, unsigned long long timeout_ns) {
   if (ctrl->done) return;
-  const int it = ctrl->iters, par = it & 1, t = threadIdx.x;
+  const int it = ctrl->iters, slot = (int)((epoch & 1) << 1) | (it & 1), t = threadIdx.x;
   const double stamp = (double)(epoch * 1048576LL + it + 1);
   __shared__ double part[4][32];
+  __shared__ int timed_out;
+  if (t == 0) timed_out = 0;
+  __syncthreads();
   if (t < world) {
-    volatile double* dst = mbox[t] + ((size_t)par * world + rank) * 8;
+    volatile double* dst = mbox[t] + ((size_t)slot * world + rank) * 8;
 #pragma unroll
     for (int i = 0; i < 4; ++i) dst[i] = ctrl->red[i];
     __threadfence_system();
     dst[4] = stamp;
-    volatile double* src = mbox[rank] + ((size_t)par * world + t) * 8;
-    const long long t0 = clock64();
-    while (src[4] != stamp)
-      if (clock64() - t0 > 4000000000LL) __trap();
+    volatile double* src = mbox[rank] + ((size_t)slot * world + t) * 8;
+    const unsigned long long t0 = global_ns();
+    bool ok = true;
+    while (src[4] != stamp) {
+      if (global_ns() - t0 > timeout_ns) { ok = false; break; }
+      __nanosleep(64);
+    }
+    if (!ok) timed_out = 1;
     __threadfence_system();
 #pragma unroll
-    for (int i = 0; i < 4; ++i) part[i][t] = src[i];
+    for (int i = 0; i < 4; ++i) part[i][t] = ok ? src[i] : 0.0;
   }
   __syncthreads();
   if (t != 0) return;
+  if (timed_out) {                                   // sticky error; the solve ends here on this rank
+    ctrl->error = NLLS_CTRL_E_PEER_TIMEOUT;
+    ctrl->done = 1;
+    return;
+  }
   double red[4] = {0.0, 0.0, 0.0, 0.0};
   for (int r = 0; r < world; ++r)
 #pragma unroll
@@ -812,10 +834,12 @@ extern "C" int nlls_iter_end(nlls_ctrl* ctrl, int solver, double ftol, void* str
 }
 
 extern "C" int nlls_iter_end_peer(nlls_ctrl* ctrl, int solver, double ftol, void* const* mailboxes, int rank, int world,
-                                  long long epoch, void* stream) {
+                                  long long epoch, double timeout_s, void* stream) {
   if (!ctrl || !mailboxes) { set_error("nlls_iter_end_peer: NULL pointer"); return NLLS_E_NULL; }
   if (world < 1 || world > 32 || rank < 0 || rank >= world) { set_error("nlls_iter_end_peer: rank %d of %d", rank, world); return NLLS_E_SHAPE; }
-  k_iter_end_peer<<<1, 32, 0, (cudaStream_t)stream>>>(ctrl, solver, ftol, (double* const*)mailboxes, rank, world, epoch);
+  if (!(timeout_s > 0.0)) timeout_s = 60.0;
+  k_iter_end_peer<<<1, 32, 0, (cudaStream_t)stream>>>(ctrl, solver, ftol, (double* const*)mailboxes, rank, world, epoch,
+                                                      (unsigned long long)(timeout_s * 1e9));
   return check_launch("nlls_iter_end_peer");
 }
 

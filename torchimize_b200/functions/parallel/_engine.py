@@ -120,8 +120,17 @@ class Workspace:
 
     def flags(self):
         """(done, iters, singular) — one small device->host read (synchronises)."""
-        d, it, sing = self.ctrl_i32[:3].tolist()
+        d, it, sing, err = self.ctrl_i32[:4].tolist()
+        self.raise_on(err)
         return d, it, sing
+
+    @staticmethod
+    def raise_on(err):
+        if err == _lib.CTRL_E_PEER_TIMEOUT:
+            raise _lib.NllsError("mode='exact-peer': a peer rank did not post its sums within the timeout (NLLS_PEER_TIMEOUT_S); "
+                                 'this rank stopped at the iteration it was waiting in — its earlier results are intact')
+        if err:
+            raise _lib.NllsError(f'device-side error flag {err} in the control block')
 
     # Fused path: the flags travel to pinned host memory behind each group of iterations and are looked at ONE group
     # late, so the device always has a full group queued while the host waits (no drain bubble between groups).  The
@@ -129,7 +138,7 @@ class Workspace:
     def post_flags(self):
         ring = _pinned_ring(self.device)
         slot = self._slot = (getattr(self, '_slot', -1) + 1) % ring.shape[0]
-        ring[slot].copy_(self.ctrl_i32[:3], non_blocking=True)
+        ring[slot].copy_(self.ctrl_i32[:4], non_blocking=True)
         ev = torch.cuda.Event()
         ev.record()
         self._pending.append((slot, ev))
@@ -139,7 +148,9 @@ class Workspace:
         while len(self._pending) > lag:
             slot, ev = self._pending.pop(0)
             ev.synchronize()
-            self._last = tuple(ring[slot].tolist())
+            d, it, sing, err = ring[slot].tolist()
+            self.raise_on(err)
+            self._last = (d, it, sing)
         return self._last
 
 
@@ -149,7 +160,7 @@ _PINNED = {}
 def _pinned_ring(device):
     key = device.index if device.index is not None else torch.cuda.current_device()
     if key not in _PINNED:
-        _PINNED[key] = torch.zeros(16, 3, dtype=torch.int32).pin_memory()
+        _PINNED[key] = torch.zeros(16, 4, dtype=torch.int32).pin_memory()
     return _PINNED[key]
 
 
@@ -159,6 +170,7 @@ def _check_p(p):
     _lib.dtype_code(p)
 
 
+@_lib.on_device_of(1)
 def solve(solver, p, function, jac_function, args, wvec, ftol, ptol, gtol, max_iter, l=1.,
           lm=None, fused=True, check_every=_GROUP, reduce_hook=None):
     """Runs one batched solve; returns the list of per-iteration snapshots (coeffs_list).
@@ -214,7 +226,8 @@ def solve(solver, p, function, jac_function, args, wvec, ftol, ptol, gtol, max_i
         """closes the iteration; multi-GPU exact mode: NCCL all-reduce of the sums, or the peer-memory kernel"""
         peer = getattr(reduce_hook, 'peer', None)
         if peer is not None:
-            _lib.call('nlls_iter_end_peer', ctrl, solver, ftol, _lib.ptr(peer.ptrs), peer.rank, peer.world, peer.epoch, st())
+            _lib.call('nlls_iter_end_peer', ctrl, solver, ftol, _lib.ptr(peer.ptrs), peer.rank, peer.world, peer.epoch,
+                      float(getattr(peer, 'timeout_s', 60.)), st())
             return
         if reduce_hook is not None:
             reduce_hook(ws.ctrl[2:6])
@@ -327,6 +340,7 @@ def solve(solver, p, function, jac_function, args, wvec, ftol, ptol, gtol, max_i
     return ws.snapshots(iters)
 
 
+@_lib.on_device_of(1)
 def plain(solver, p, function, jac_function, wvec, l, max_iter):
     """Fixed-iteration variants (gna:94-117, gda:90-113): no stop tests, returns the final p."""
     _check_p(p)

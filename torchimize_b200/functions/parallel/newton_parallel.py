@@ -7,6 +7,7 @@ from ... import _lib
 from ._engine import _as_work
 
 
+@_lib.on_device_of(0)
 def newton_step_parallel(p: torch.Tensor, function: Callable, jac_function: Callable, wvec: torch.Tensor
                          ) -> Tuple[torch.Tensor, torch.Tensor, torch.Tensor, torch.Tensor]:
     """Builds g = sum_c w_c J^T f and H = sum_c w_c J^T J with ONE fused pass over J (K1,

@@ -106,6 +106,7 @@ def stop(gc, hc, pc, ff, sd, ftol, ptol, gtol, f_gate=True):
     return bool(gcon) or bool(pcon) or bool(fcon)
 
 
+@_lib.on_device_of(0)
 def lsq_lma(p, function, jac_function, args, ftol, ptol, gtol, tau, meth, rho1, rho2, bet, gam, max_iter):
     S = Single(p)
     fun, jac = bind(function, jac_function, args)
@@ -150,6 +151,7 @@ def lsq_lma(p, function, jac_function, args, ftol, ptol, gtol, tau, meth, rho1, 
     return out
 
 
+@_lib.on_device_of(0)
 def _newton_like(p, function, jac_function, args, ftol, ptol, gtol, l, max_iter, tall):
     """lsq_gna (gna_fun_single.py:59-84: h = -l solve(H, g)) and gradient_descent (gda_fun_single.py:58-81: h = -l lstsq(j, f),
     here through the fp64 normal equations of the tall system)."""

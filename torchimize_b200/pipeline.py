@@ -100,10 +100,11 @@ def solve_host_batches(solver, batches, function, jac_function=None, wvec=None, 
             return
         s = slots[pending.pop(0)]
         compute.wait_event(s.ready)
-        coeffs = solver(s.p, function, jac_function, args=tuple(s.args), wvec=wvec, **solver_kw)
-        s.out.copy_(s.p, non_blocking=True)
-        s.free = torch.cuda.Event()
-        s.free.record(compute)
+        with torch.cuda.device(device):              # the solver launches on the current device's stream
+            coeffs = solver(s.p, function, jac_function, args=tuple(s.args), wvec=wvec, **solver_kw)
+            s.out.copy_(s.p, non_blocking=True)
+            s.free = torch.cuda.Event()
+            s.free.record(compute)
         # top the pipe up BEFORE blocking on this batch's result, so the next copy is already running
         while not exhausted and len(pending) < depth - 1:
             enqueue_copy()

@@ -12,6 +12,8 @@ Problems are independent, so B is split into contiguous shards, one process per 
                 32 bytes + a stamp straight into the peers' mailboxes over NVLink (symmetric memory) and
                 sums what it received — no collective library call inside the iteration.
 """
+import os
+
 import torch
 import torch.distributed as dist
 
@@ -47,11 +49,13 @@ class PeerExchange:
         if self.world > 32:
             raise ValueError('PeerExchange: at most 32 ranks')
         dev = torch.device('cuda', torch.cuda.current_device())
-        self.buf = symm_mem.empty(2 * self.world * 8, dtype=torch.float64, device=dev)
+        self.buf = symm_mem.empty(4 * self.world * 8, dtype=torch.float64, device=dev)   # [2 epoch parities][2 iteration parities][world][8]
         self.buf.zero_()
         self.handle = symm_mem.rendezvous(self.buf, group=group.group_name)
         self.ptrs = torch.tensor([int(q) for q in self.handle.buffer_ptrs], dtype=torch.int64, device=dev)
         self.epoch = 0
+        self.group = group
+        self.timeout_s = float(os.environ.get('NLLS_PEER_TIMEOUT_S', '60'))   # a silent peer sets ctrl->error after this long
         torch.cuda.synchronize()
         dist.barrier(group)                                  # every mailbox is zeroed before anybody writes into a peer
 
@@ -108,6 +112,10 @@ def solve_sharded(solver_fn, p_local, function, jac_function=None, args=(), wvec
     if hook is None:
         coeffs = solver_fn(p_local, function, jac_function, args=args, wvec=wvec, **kw)
     else:
+        if getattr(hook, 'peer', None) is not None:
+            # align the ranks before the first stamp: whatever a rank did before this call (data loading, a plugin
+            # compile, a GC pause) must not count against the peers' timeout
+            dist.barrier(group)
         token = _engine.set_default_reduce_hook(hook)
         try:
             coeffs = solver_fn(p_local, function, jac_function, args=args, wvec=wvec, **kw)
