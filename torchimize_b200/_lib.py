@@ -89,6 +89,19 @@ def load():
     return _lib
 
 
+def source_hash():
+    """sha1 (16 hex digits) of the kernel sources and the C-ABI header: identifies the build an ncu capture belongs to"""
+    import hashlib
+    h = hashlib.sha1()
+    for fn in sorted(os.listdir(CSRC)):
+        if fn.endswith(('.cu', '.cuh')) or fn == 'Makefile':
+            with open(os.path.join(CSRC, fn), 'rb') as f:
+                h.update(f.read())
+    with open(os.path.join(_HERE, '..', 'include', 'nlls_b200.h'), 'rb') as f:
+        h.update(f.read())
+    return h.hexdigest()[:16]
+
+
 JIT_DIR = os.path.join(_HERE, '_jit')
 PLUGIN_ENTRY_POINTS = ('nlls_model_eval', 'nlls_model_normal_eq', 'nlls_model_normal_eq_gda', 'nlls_model_cost_stat',
                        'nlls_model_lm_trial')
