@@ -27,7 +27,8 @@
 extern "C" {
 #endif
 
-#define NLLS_B200_ABI_VERSION 2   /* 2: the fused kernels keep the model value m [B,N] between iterations, not f [B,C,N] */
+#define NLLS_B200_ABI_VERSION 2   /* 2: the fused kernels keep the model value m [B,N] between iterations, not f [B,C,N];
+                                     per-problem tracking / retirement (nlls_track) */
 
 enum { NLLS_F32 = 0, NLLS_F64 = 1 };
 
@@ -63,6 +64,34 @@ typedef struct nlls_ctrl {
   int error;         /* sticky: NLLS_CTRL_E_* set by a kernel (0 = none); done is set with it */
   double red[4];
 } nlls_ctrl;
+
+/* Per-problem tracking and retirement (north_star kernel 3).  SURVEY 3.7 Q1: the reference's masked copy
+ * `p[~converged] = pn[~converged]` (lma:115, gna:85, gda:81) was meant to freeze converged problems and is a no-op, so
+ * every problem keeps stepping until ALL have converged in the same iteration.  The default (track == NULL, or
+ * retire == 0) reproduces that.  Device pointers, host struct:
+ *   pstat [B,4] int32, initialise every row to {-1,0,0,0}:
+ *     [0] first iteration at which the problem's OWN stop test fired, -1 = not yet.  Own test = gcon | pcon | fcon with
+ *         per-problem gates: LM's fcon counts only in an iteration whose step this problem accepted (the reference's
+ *         batch-global gate lma:110 made per problem), GD's fcon uses the problem's own two sums instead of gda:76's
+ *         batch totals
+ *     [1] the reasons at that iteration: 1 = gcon, 2 = pcon, 4 = fcon
+ *     [2] LM: accepted steps so far; GN / GD: steps taken
+ *     [3] flags: 1 = a non-finite step was produced
+ *   retire == 0: pstat is recorded, nothing else changes.
+ *   retire != 0: a problem with pstat[0] >= 0 is frozen at the iterate it had when its test fired (== the snapshot of
+ *     that iteration of a reference-semantics run: per-problem arithmetic does not depend on the batch).  K2 / K3 skip it
+ *     (its snapshot repeats), the fused model kernels never evaluate it again: iteration k (= ctrl->iters) walks
+ *     active[k & 1][0 .. count[k & 1]) and its update kernel appends the problems that stay active to
+ *     active[(k+1) & 1] (order arbitrary, results independent of it); nlls_iter_end clears the consumed count and sets
+ *     ctrl->done when no problem is left — no host round-trip anywhere.  Initialise active[0] = 0..B-1, count = {B, 0}. */
+typedef struct nlls_track {
+  int* pstat;        /* [B,4] */
+  int* active;       /* [2,B] */
+  int* count;        /* [2] */
+  int retire;
+  int reserved;
+  long long B;
+} nlls_track;
 
 /* ---- housekeeping ---------------------------------------------------------------- */
 int nlls_abi_version(void);
@@ -106,7 +135,7 @@ int nlls_cost_stat(int dtype, const void* f, long long B, int C, int N, double* 
  * Cholesky in registers, LU with partial pivoting when a pivot is not positive.  */
 int nlls_lm_solve(int dtype, const void* g, const void* H, const void* p, const void* u,
                   void* dscale, int marquardt, long long B, int P,
-                  void* h, void* p_trial, nlls_ctrl* ctrl, void* stream);
+                  void* h, void* p_trial, nlls_ctrl* ctrl, const nlls_track* track /*nullable*/, void* stream);
 
 /* ---- K3: update / gain ratio / damping adaptation / stop tests ----------------------
  * LM (lma:100-116, 124-152): rho from stats[b][0] - stat_h[b] and h^T(u h - g); Nielsen or
@@ -117,13 +146,13 @@ int nlls_lm_update(int dtype, void* p, const void* h, const void* g, void* u, vo
                    double rho1, double rho2, double beta, double gama,
                    double ftol, double ptol, double gtol,
                    long long B, int P, void* p_hist, void* rho_out /*nullable*/,
-                   nlls_ctrl* ctrl, void* stream);
+                   nlls_ctrl* ctrl, const nlls_track* track /*nullable*/, void* stream);
 
 /* GN (gna:139-141, 78-86): h = solve_fp64(H, g); p -= l*h; stop tests; snapshot. */
 int nlls_gn_update(int dtype, void* p, const void* g, const void* H, const double* stats,
                    double l, double ftol, double ptol, double gtol, int with_masks,
                    long long B, int P, void* h_out /*nullable*/, void* p_hist /*nullable*/,
-                   nlls_ctrl* ctrl, void* stream);
+                   nlls_ctrl* ctrl, const nlls_track* track /*nullable*/, void* stream);
 
 /* GD (gda:139-146, 71-82): h = solve_fp64(H64, g64) (== lstsq(j_s, f_s)); p -= l*h; g = h/l;
  * gcon/pcon per problem; the batch-global fcon sums (Q5) are reduced deterministically
@@ -131,12 +160,12 @@ int nlls_gn_update(int dtype, void* p, const void* g, const void* H, const doubl
 int nlls_gd_update(int dtype, void* p, const double* g64, const double* H64, const double* stats,
                    double l, double ftol, double ptol, double gtol, int with_masks,
                    long long B, int P, void* h_out /*nullable*/, void* p_hist /*nullable*/,
-                   nlls_ctrl* ctrl, void* stream);
+                   nlls_ctrl* ctrl, const nlls_track* track /*nullable*/, void* stream);
 
 /* Closes an iteration: decides ctrl->done from ctrl->red (per `solver`), ++ctrl->iters,
  * clears red.  have to run after the update kernel (and after the all-reduce of red in a
  * multi-GPU exact run).  */
-int nlls_iter_end(nlls_ctrl* ctrl, int solver, double ftol, void* stream);
+int nlls_iter_end(nlls_ctrl* ctrl, int solver, double ftol, const nlls_track* track /*nullable*/, void* stream);
 
 /* nlls_iter_end for a batch sharded over the GPUs of one box in "exact" mode (lma:110,118, gna:88, gda:76,84 see the
  * WHOLE batch): sums ctrl->red over the ranks through peer-mapped mailboxes (NVLink P2P stores + stamp, no collective
@@ -179,7 +208,7 @@ int nlls_model_normal_eq(int model, int dtype, const void* p, int P, const void*
                          long long y_bstride, long long y_cstride,
                          const void* wvec, int wlen, long long B, int C, int N,
                          void* m_pp0, void* m_pp1, void* g, void* H, double* stats,
-                         const nlls_ctrl* ctrl, void* stream);
+                         const nlls_ctrl* ctrl, const nlls_track* track /*nullable*/, void* stream);
 
 /* Speculative Levenberg-Marquardt trial evaluation (fused path): ONE pass at the trial point p + h that yields
  * both halves of what lma:99-100 and the NEXT iteration's newton_parallel.py:38-43 need:
@@ -194,7 +223,8 @@ int nlls_model_normal_eq(int model, int dtype, const void* p, int P, const void*
 int nlls_model_lm_trial(int model, int dtype, const void* p_trial, int P, const void* x, const void* y,
                         long long y_bstride, long long y_cstride, const void* wvec, int wlen,
                         long long B, int C, int N, void* m_buf0, void* m_buf1, const unsigned char* sel,
-                        void* g_t, void* H_t, double* stats_t, const nlls_ctrl* ctrl, void* stream);
+                        void* g_t, void* H_t, double* stats_t, const nlls_ctrl* ctrl,
+                        const nlls_track* track /*nullable*/, void* stream);
 
 /* K3 for the speculative schedule (lma:100-116, 124-152): as nlls_lm_update, with
  *   rho numerator  = stats[b][0] - stats_t[b][0];
@@ -206,14 +236,14 @@ int nlls_lm_update_spec(int dtype, void* p, const void* h, void* g, void* H, con
                         double rho1, double rho2, double beta, double gama,
                         double ftol, double ptol, double gtol,
                         long long B, int P, void* p_hist, void* rho_out /*nullable*/,
-                        nlls_ctrl* ctrl, void* stream);
+                        nlls_ctrl* ctrl, const nlls_track* track /*nullable*/, void* stream);
 
 /* GD flavour of the fused kernel: outputs as nlls_normal_eq_gda; fsum_pp are [B,N] ping-pong. */
 int nlls_model_normal_eq_gda(int model, int dtype, const void* p, int P, const void* x, const void* y,
                              long long y_bstride, long long y_cstride,
                              const void* wvec, int wlen, long long B, int C, int N,
                              void* fsum_pp0, void* fsum_pp1, double* g64, double* H64, double* stats,
-                             const nlls_ctrl* ctrl, void* stream);
+                             const nlls_ctrl* ctrl, const nlls_track* track /*nullable*/, void* stream);
 
 /* stat_out[b] = sum_c (sum_n f(p_trial)[b,c,n])^2 without materialising f (lma:99-100). */
 int nlls_model_cost_stat(int model, int dtype, const void* p_trial, int P, const void* x, const void* y,

@@ -47,9 +47,9 @@ def test_argument_validation_needs_no_device():
     assert rc == -2
     rc = lib.nlls_normal_eq(_lib.F64, None, None, None, None, 1, 4, 1, 8, 4, None, None, None, None, None)
     assert rc == -3
-    rc = lib.nlls_model_normal_eq(9, _lib.F64, 8, 4, 8, 8, 1, 0, 8, 1, 1, 1, 4, None, None, 8, 8, 8, None, None)
+    rc = lib.nlls_model_normal_eq(9, _lib.F64, 8, 4, 8, 8, 1, 0, 8, 1, 1, 1, 4, None, None, 8, 8, 8, None, None, None)
     assert rc == -5
-    assert lib.nlls_iter_end(None, 0, 0.0, None) == -3
+    assert lib.nlls_iter_end(None, 0, 0.0, None, None) == -3
 
 
 def test_product_refuses_cpu_tensors():

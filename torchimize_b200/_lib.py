@@ -21,6 +21,17 @@ CTRL_E_PEER_TIMEOUT = 1
 
 _vp, _i, _ll, _d = ctypes.c_void_p, ctypes.c_int, ctypes.c_longlong, ctypes.c_double
 
+
+class Track(ctypes.Structure):
+    """nlls_track (include/nlls_b200.h): per-problem tracking / retirement; device pointers in a host struct"""
+    _fields_ = [('pstat', _vp), ('active', _vp), ('count', _vp), ('retire', _i), ('reserved', _i), ('B', _ll)]
+
+
+_tp = ctypes.POINTER(Track)
+# entry points that take `const nlls_track* track` as their last argument before `stream`; call() inserts it (track=None: none)
+TRACKED = ('nlls_lm_solve', 'nlls_lm_update', 'nlls_gn_update', 'nlls_gd_update', 'nlls_iter_end', 'nlls_model_normal_eq',
+           'nlls_model_normal_eq_gda', 'nlls_model_lm_trial', 'nlls_lm_update_spec')
+
 # name -> argtypes; mirrors include/nlls_b200.h one to one (tests check the exported symbols)
 SIGNATURES = {
     'nlls_abi_version': [],
@@ -29,21 +40,21 @@ SIGNATURES = {
     'nlls_normal_eq': [_i, _vp, _vp, _vp, _vp, _i, _ll, _i, _i, _i, _vp, _vp, _vp, _vp, _vp],
     'nlls_normal_eq_gda': [_i, _vp, _vp, _vp, _vp, _i, _ll, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp],
     'nlls_cost_stat': [_i, _vp, _ll, _i, _i, _vp, _vp, _vp],
-    'nlls_lm_solve': [_i, _vp, _vp, _vp, _vp, _vp, _i, _ll, _i, _vp, _vp, _vp, _vp],
-    'nlls_lm_update': [_i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _d, _d, _d, _d, _d, _d, _d, _ll, _i, _vp, _vp, _vp, _vp],
-    'nlls_gn_update': [_i, _vp, _vp, _vp, _vp, _d, _d, _d, _d, _i, _ll, _i, _vp, _vp, _vp, _vp],
-    'nlls_gd_update': [_i, _vp, _vp, _vp, _vp, _d, _d, _d, _d, _i, _ll, _i, _vp, _vp, _vp, _vp],
-    'nlls_iter_end': [_vp, _i, _d, _vp],
+    'nlls_lm_solve': [_i, _vp, _vp, _vp, _vp, _vp, _i, _ll, _i, _vp, _vp, _vp, _tp, _vp],
+    'nlls_lm_update': [_i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _d, _d, _d, _d, _d, _d, _d, _ll, _i, _vp, _vp, _vp, _tp, _vp],
+    'nlls_gn_update': [_i, _vp, _vp, _vp, _vp, _d, _d, _d, _d, _i, _ll, _i, _vp, _vp, _vp, _tp, _vp],
+    'nlls_gd_update': [_i, _vp, _vp, _vp, _vp, _d, _d, _d, _d, _i, _ll, _i, _vp, _vp, _vp, _tp, _vp],
+    'nlls_iter_end': [_vp, _i, _d, _tp, _vp],
     'nlls_iter_end_peer': [_vp, _i, _d, _vp, _i, _i, _ll, _d, _vp],
     'nlls_sumsq_partials': [],
     'nlls_sumsq': [_i, _vp, _vp, _ll, _vp, _vp],
     'nlls_model_eval': [_i, _i, _vp, _i, _vp, _vp, _ll, _ll, _ll, _i, _i, _vp, _vp, _vp, _vp],
-    'nlls_model_normal_eq': [_i, _i, _vp, _i, _vp, _vp, _ll, _ll, _vp, _i, _ll, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp],
-    'nlls_model_normal_eq_gda': [_i, _i, _vp, _i, _vp, _vp, _ll, _ll, _vp, _i, _ll, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp],
+    'nlls_model_normal_eq': [_i, _i, _vp, _i, _vp, _vp, _ll, _ll, _vp, _i, _ll, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _tp, _vp],
+    'nlls_model_normal_eq_gda': [_i, _i, _vp, _i, _vp, _vp, _ll, _ll, _vp, _i, _ll, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _tp, _vp],
     'nlls_model_cost_stat': [_i, _i, _vp, _i, _vp, _vp, _ll, _ll, _ll, _i, _i, _vp, _vp, _vp],
-    'nlls_model_lm_trial': [_i, _i, _vp, _i, _vp, _vp, _ll, _ll, _vp, _i, _ll, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp],
+    'nlls_model_lm_trial': [_i, _i, _vp, _i, _vp, _vp, _ll, _ll, _vp, _i, _ll, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _tp, _vp],
     'nlls_lm_update_spec': [_i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _d, _d, _d, _d, _d, _d, _d, _ll, _i,
-                            _vp, _vp, _vp, _vp],
+                            _vp, _vp, _vp, _tp, _vp],
 }
 
 _lock = threading.Lock()
@@ -221,11 +232,14 @@ def timing_records():
     return [(n, a.elapsed_time(b)) for n, a, b in (_timing or [])]
 
 
-def call(name, *args, lib=None):
+def call(name, *args, lib=None, track=None):
     """Invoke an entry point on the current stream of the current device; raise on error.
-    lib: a plugin library handle (load_plugin) for the nlls_model_* entry points of a user model."""
+    lib: a plugin library handle (load_plugin) for the nlls_model_* entry points of a user model.
+    track: a Track (nlls_track) for the entry points in TRACKED — inserted before their `stream` argument (None = none)."""
     global launches
     lib = lib or load()
+    if name in TRACKED:
+        args = args[:-1] + (ctypes.byref(track) if track is not None else None, args[-1])
     if _timing is not None:
         a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         a.record()

@@ -38,6 +38,37 @@ __device__ __forceinline__ int iter_index(const nlls_ctrl* ctrl) {
   return ctrl ? *reinterpret_cast<const volatile int*>(&ctrl->iters) : 0;
 }
 
+// ---- per-problem tracking / retirement (nlls_track, include/nlls_b200.h)
+__device__ __forceinline__ bool track_frozen(const nlls_track& tr, long long b) { return tr.retire && tr.pstat[b * 4] >= 0; }
+__device__ __forceinline__ void track_record(const nlls_track& tr, long long b, bool conv, int reason, int step_inc, bool nonfinite,
+                                             int it) {
+  int* s = tr.pstat + b * 4;
+  if (conv && s[0] < 0) { s[0] = it; s[1] = reason; }
+  if (step_inc) s[2] += step_inc;
+  if (nonfinite) s[3] |= 1;
+}
+// every lane of the warp has to call it: the problems that stay active go to the NEXT iteration's list (warp-aggregated)
+__device__ __forceinline__ void track_append(const nlls_track& tr, int it, long long b, bool keep) {
+  const unsigned m = __ballot_sync(0xffffffffu, keep);
+  if (!m) return;
+  const int lane = threadIdx.x & 31, leader = __ffs(m) - 1;
+  int base = 0;
+  if (lane == leader) base = atomicAdd(tr.count + ((it + 1) & 1), __popc(m));
+  base = __shfl_sync(0xffffffffu, base, leader);
+  if (keep) tr.active[(size_t)((it + 1) & 1) * tr.B + base + __popc(m & ((1u << lane) - 1))] = (int)b;
+}
+// the problems a fused model kernel walks: all of them, or this iteration's list of active ones
+struct WorkList {
+  const int* list;
+  long long n;
+  __device__ __forceinline__ WorkList(const nlls_track& tr, int it, long long B) {
+    if (tr.retire) { list = tr.active + (size_t)(it & 1) * tr.B; n = tr.count[it & 1]; }
+    else { list = nullptr; n = B; }
+  }
+  __device__ __forceinline__ long long at(long long i) const { return list ? (long long)list[i] : i; }
+};
+inline nlls_track track_or_none(const nlls_track* t) { nlls_track z{}; return t ? *t : z; }
+
 template <typename T> __device__ __forceinline__ T shfl_xor(T v, int m) { return __shfl_xor_sync(0xffffffffu, v, m); }
 template <typename T> __device__ __forceinline__ T shfl_down(T v, int d) { return __shfl_down_sync(0xffffffffu, v, d); }
 

@@ -46,10 +46,11 @@ __global__ void __launch_bounds__(TPB)
 k_model_normal_eq(const T* __restrict__ p, const T* __restrict__ x, const T* __restrict__ y, long long ybs,
                   long long ycs, const T* __restrict__ w, int wlen, long long B, int C, int N, T* mA, T* mB,
                   T* __restrict__ g, T* __restrict__ H, double* __restrict__ stats, const nlls_ctrl* ctrl,
-                  const unsigned char* __restrict__ sel) {
+                  const unsigned char* __restrict__ sel, nlls_track tr) {
   if (is_done(ctrl)) return;
   constexpr int P = Model::P, NW = TPB / 32, NH = Tri<P>::N, V = P + NH + 2;
   const int it = iter_index(ctrl);
+  const WorkList WL(tr, it, B);
   // sel == NULL: buffers alternate with the iteration parity.  sel != NULL (speculative LM trial evaluation):
   // problem b's current model values live in (sel[b] ? mB : mA) and the trial values go to the other buffer.
   T* m_out = (it & 1) ? mB : mA;
@@ -60,7 +61,8 @@ k_model_normal_eq(const T* __restrict__ p, const T* __restrict__ x, const T* __r
   double* sfw = sfc + (size_t)C * TPB; // [C][NW]
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
 
-  for (long long b = blockIdx.x; b < B; b += gridDim.x) {
+  for (long long wi = blockIdx.x; wi < WL.n; wi += gridDim.x) {
+    const long long b = WL.at(wi);
     if (sel) { const bool sb = sel[b] != 0; m_prev = sb ? mB : mA; m_out = sb ? mA : mB; }
     Model M;
     M.load(p + b * P);
@@ -170,22 +172,24 @@ struct TileRing {
   T* ring;
   uint64_t* bars;
   const T *a, *bsrc;
-  long long a_bs, a_rs, b_bs, b_rs, B;
+  long long a_bs, a_rs, b_bs, b_rs;
   int nA, nB, N, stage_elems;
+  const int* wlist;      // work list (retire mode) or NULL = every problem
+  long long wn, pw;      // work items, producer: next work index
   long long pb;          // producer: next problem
   int pn0, pst;          // producer: next sample offset, next stage
   int st;                // consumer: current stage
   unsigned ph;           // consumer: current parity
   __device__ __forceinline__ void init(unsigned char* smem, const T* a_, long long a_bs_, long long a_rs_, int nA_,
-                                       const T* b_, long long b_bs_, long long b_rs_, int nB_, long long B_, int N_) {
+                                       const T* b_, long long b_bs_, long long b_rs_, int nB_, const WorkList& WL, int N_) {
     a = a_; a_bs = a_bs_; a_rs = a_rs_; nA = nA_;
     bsrc = b_; b_bs = b_bs_; b_rs = b_rs_; nB = b_ ? nB_ : 0;
-    B = B_; N = N_;
+    wlist = WL.list; wn = WL.n; N = N_;
     stage_elems = (nA_ + nB_) * TN;                          // fixed layout even when set B is absent
     ring = reinterpret_cast<T*>(smem);
     size_t off = ((size_t)NSTAGE * stage_elems * sizeof(T) + 15) & ~(size_t)15;
     bars = reinterpret_cast<uint64_t*>(smem + off);
-    pb = blockIdx.x; pn0 = 0; pst = 0; st = 0; ph = 0;
+    pw = blockIdx.x; pb = pw < wn ? (wlist ? (long long)wlist[pw] : pw) : 0; pn0 = 0; pst = 0; st = 0; ph = 0;
     if (threadIdx.x == 0) {
 #pragma unroll
       for (int s = 0; s < NSTAGE; ++s) mbar_init(&bars[s], 1);
@@ -201,7 +205,7 @@ struct TileRing {
     return (((size_t)NSTAGE * (nA_ + nB_) * TN * sizeof(T) + 15) & ~(size_t)15) + 64;
   }
   __device__ __forceinline__ void issue() {                  // thread 0 only, after the stage was handed back
-    if (pb >= B) return;
+    if (pw >= wn) return;
     const int rows = min(TN, N - pn0);
     const unsigned nbytes = (unsigned)rows * (unsigned)sizeof(T);
     T* dst = ring + (size_t)pst * stage_elems;
@@ -214,7 +218,7 @@ struct TileRing {
       for (int r = 0; r < nB; ++r, s2 += b_rs, dst += TN) bulk_g2s(dst, s2, nbytes, bar);
     }
     pn0 += TN;
-    if (pn0 >= N) { pn0 = 0; pb += gridDim.x; }
+    if (pn0 >= N) { pn0 = 0; pw += gridDim.x; pb = pw < wn ? (wlist ? (long long)wlist[pw] : pw) : 0; }
     pst = (pst + 1 == NSTAGE) ? 0 : pst + 1;
   }
   __device__ __forceinline__ const T* wait() {               // all threads; returns the stage base
@@ -242,13 +246,14 @@ __global__ void __launch_bounds__(TPB, MINB > 0 ? MINB : 512 / TPB)
 k_model_normal_eq_staged(const T* __restrict__ p, const T* __restrict__ x, const T* __restrict__ y, long long ybs,
                          long long ycs, const T* __restrict__ w, int wlen, long long B, int C_, int N, T* mA, T* mB,
                          T* __restrict__ g, T* __restrict__ H, double* __restrict__ stats, const nlls_ctrl* ctrl,
-                         const unsigned char* __restrict__ sel) {
+                         const unsigned char* __restrict__ sel, nlls_track tr) {
   if (is_done(ctrl)) return;
   constexpr int P = Model::P, NW = TPB / 32, NH = Tri<P>::N, V = P + NH + 2, TN = TPB * S;
   constexpr int VP = Pow2Ceil<V>::value, OWN = 32 / VP;      // transposed reduction: lane L owns value L / OWN
   static_assert(V <= 32, "model with too many parameters for the transposed reduction");
   const int C = CT > 0 ? CT : C_;
   const int it = iter_index(ctrl);
+  const WorkList WL(tr, it, B);
   T* m_out = (it & 1) ? mB : mA;
   const T* m_prev = (it > 0 && mA) ? ((it & 1) ? mA : mB) : nullptr;
   const bool has_prev = m_prev != nullptr || sel != nullptr;  // sel: per-problem buffer roles (see k_model_normal_eq)
@@ -271,11 +276,11 @@ k_model_normal_eq_staged(const T* __restrict__ p, const T* __restrict__ x, const
   __syncthreads();
 
   // ---- producer state (thread 0): next tile to issue = (problem pb, sample offset pn0) into stage pst
-  long long pb = blockIdx.x;
+  long long pw = blockIdx.x, pb = pw < WL.n ? WL.at(pw) : 0;   // producer: work index, problem
   int pn0 = 0, pst = 0;
-  unsigned char psel = (sel && tid == 0 && pb < B) ? sel[pb] : (unsigned char)0;
+  unsigned char psel = (sel && tid == 0 && pw < WL.n) ? sel[pb] : (unsigned char)0;
   auto issue = [&]() {
-    if (pb >= B) return;
+    if (pw >= WL.n) return;
     const int rows = min(TN, N - pn0);
     const unsigned bytes = (unsigned)rows * (unsigned)sizeof(T);
     T* dst = ring + (size_t)pst * stage_elems;
@@ -287,8 +292,9 @@ k_model_normal_eq_staged(const T* __restrict__ p, const T* __restrict__ x, const
     pn0 += TN;
     if (pn0 >= N) {
       pn0 = 0;
-      pb += gridDim.x;
-      if (sel && pb < B) psel = sel[pb];                     // buffer role of the NEXT problem: in flight until its first tile
+      pw += gridDim.x;
+      pb = pw < WL.n ? WL.at(pw) : 0;
+      if (sel && pw < WL.n) psel = sel[pb];                     // buffer role of the NEXT problem: in flight until its first tile
     }
     pst = (pst + 1 == NSTAGE) ? 0 : pst + 1;
   };
@@ -299,10 +305,11 @@ k_model_normal_eq_staged(const T* __restrict__ p, const T* __restrict__ x, const
 
   int st = 0, pbuf = 0;
   unsigned ph = 0;
-  for (long long b = blockIdx.x; b < B; b += gridDim.x, pbuf ^= 1) {
+  for (long long wi = blockIdx.x; wi < WL.n; wi += gridDim.x, pbuf ^= 1) {
+    const long long b = WL.at(wi);
     Model M;
     M.load(p + b * P);
-    if (tid == 0 && b + gridDim.x < B) prefetch_l1(p + (b + gridDim.x) * P);   // next problem's parameters
+    if (tid == 0 && wi + gridDim.x < WL.n) prefetch_l1(p + WL.at(wi + gridDim.x) * P);   // next problem's parameters
     RowAcc<T, P> acc;
     acc.clear();
     double sd = 0.0, sq = 0.0;
@@ -472,12 +479,13 @@ __global__ void __launch_bounds__(TPB, 512 / TPB)
 k_model_normal_eq_vec(const T* __restrict__ p, const T* __restrict__ x, const T* __restrict__ y, long long ybs,
                       long long ycs, const T* __restrict__ w, int wlen, long long B, int C, int N, T* mA, T* mB,
                       T* __restrict__ g, T* __restrict__ H, double* __restrict__ stats, const nlls_ctrl* ctrl,
-                      const unsigned char* __restrict__ sel) {
+                      const unsigned char* __restrict__ sel, nlls_track tr) {
   if (is_done(ctrl)) return;
   constexpr int P = Model::P, NW = TPB / 32, NH = Tri<P>::N, V = P + NH + 2, VEC = Lane16<T>::VEC, TN = TPB * VEC;
   constexpr int VP = Pow2Ceil<V>::value, OWN = 32 / VP;
   static_assert(V <= 32, "model with too many parameters for the transposed reduction");
   const int it = iter_index(ctrl);
+  const WorkList WL(tr, it, B);
   T* m_out = (it & 1) ? mB : mA;
   const T* m_prev = (it > 0 && mA) ? ((it & 1) ? mA : mB) : nullptr;
   const bool has_prev = m_prev != nullptr || sel != nullptr;
@@ -499,11 +507,11 @@ k_model_normal_eq_vec(const T* __restrict__ p, const T* __restrict__ x, const T*
   }
   __syncthreads();
 
-  long long pb = blockIdx.x;
+  long long pw = blockIdx.x, pb = pw < WL.n ? WL.at(pw) : 0;   // producer: work index, problem
   int pn0 = 0, pst = 0;
-  unsigned char psel = (sel && tid == 0 && pb < B) ? sel[pb] : (unsigned char)0;
+  unsigned char psel = (sel && tid == 0 && pw < WL.n) ? sel[pb] : (unsigned char)0;
   auto issue = [&]() {
-    if (pb >= B) return;
+    if (pw >= WL.n) return;
     const int rows = min(TN, N - pn0);
     const unsigned bytes = (unsigned)rows * (unsigned)sizeof(T);
     T* dst = ring + (size_t)pst * stage_elems;
@@ -515,8 +523,9 @@ k_model_normal_eq_vec(const T* __restrict__ p, const T* __restrict__ x, const T*
     pn0 += TN;
     if (pn0 >= N) {
       pn0 = 0;
-      pb += gridDim.x;
-      if (sel && pb < B) psel = sel[pb];                     // buffer role of the NEXT problem: in flight until its first tile
+      pw += gridDim.x;
+      pb = pw < WL.n ? WL.at(pw) : 0;
+      if (sel && pw < WL.n) psel = sel[pb];                     // buffer role of the NEXT problem: in flight until its first tile
     }
     pst = (pst + 1 == NSTAGE) ? 0 : pst + 1;
   };
@@ -528,10 +537,11 @@ k_model_normal_eq_vec(const T* __restrict__ p, const T* __restrict__ x, const T*
   int st = 0, pbuf = 0;
   unsigned ph = 0;
   const int ystep = (Cy == 1) ? 0 : TN;
-  for (long long b = blockIdx.x; b < B; b += gridDim.x, pbuf ^= 1) {
+  for (long long wi = blockIdx.x; wi < WL.n; wi += gridDim.x, pbuf ^= 1) {
+    const long long b = WL.at(wi);
     Model M;
     M.load(p + b * P);
-    if (tid == 0 && b + gridDim.x < B) prefetch_l1(p + (b + gridDim.x) * P);
+    if (tid == 0 && wi + gridDim.x < WL.n) prefetch_l1(p + WL.at(wi + gridDim.x) * P);
     RowAcc<T, P> acc;
     acc.clear();
     double sd = 0.0, sq = 0.0;
@@ -655,7 +665,7 @@ __global__ void __launch_bounds__(NW * 32)
 k_model_wpp(const T* __restrict__ p, const T* __restrict__ x, const T* __restrict__ y, long long ybs, long long ycs,
             const T* __restrict__ w, int wlen, long long B, int C_, int N, T* prevA, T* prevB, void* __restrict__ outg,
             void* __restrict__ outH, double* __restrict__ stats, const nlls_ctrl* ctrl, int CH,
-            const unsigned char* __restrict__ sel) {
+            const unsigned char* __restrict__ sel, nlls_track tr) {
   if (is_done(ctrl)) return;
   using TA = typename std::conditional<MODE == WPP_GDA, double, T>::type;      // accumulator type of g / H
   constexpr int P = Model::P, NH = Tri<P>::N, V = P + NH;
@@ -668,6 +678,7 @@ k_model_wpp(const T* __restrict__ p, const T* __restrict__ x, const T* __restric
   constexpr int ISTR = VL ? 1 : 32;          // distance between a lane's consecutive samples
   const int C = C1 ? 1 : C_;                 // C1: single cost — no cost loop, per-cost sums in a register
   const int it = iter_index(ctrl);
+  const WorkList WL(tr, it, B);
   T* f_out = (MODE == WPP_COST) ? nullptr : ((it & 1) ? prevB : prevA);
   const T* f_prev = (MODE != WPP_COST && it > 0 && prevA) ? ((it & 1) ? prevA : prevB) : nullptr;
   const bool has_prev = f_prev != nullptr || sel != nullptr;  // sel (NEQ only): per-problem buffer roles
@@ -694,12 +705,12 @@ k_model_wpp(const T* __restrict__ p, const T* __restrict__ x, const T* __restric
   const int QN = (N + CH - 1) / CH;
   const long long prev_bs = (long long)N;                                      // problem stride of prev / f_out
 
-  long long fb = wid;                       // producer cursor: next chunk to request
+  long long fw = wid, fb = fw < WL.n ? WL.at(fw) : 0;   // producer cursor: work index / problem of the next chunk to request
   int fq = 0;
   unsigned fst = 0;
-  unsigned char fsel = (sel && lane == 0 && fb < B) ? sel[fb] : (unsigned char)0;
+  unsigned char fsel = (sel && lane == 0 && fw < WL.n) ? sel[fb] : (unsigned char)0;
   auto issue = [&]() {
-    if (fb >= B) return;
+    if (fw >= WL.n) return;
     if (lane == 0) {
       const int n0 = fq * CH;
       const unsigned bytes = (unsigned)min(CH, N - n0) * (unsigned)sizeof(T);
@@ -715,8 +726,9 @@ k_model_wpp(const T* __restrict__ p, const T* __restrict__ x, const T* __restric
     fst = (fst + 1 == NSTAGE) ? 0 : fst + 1;
     if (++fq == QN) {
       fq = 0;
-      fb += nwarps;
-      if (sel && lane == 0 && fb < B) fsel = sel[fb];        // next problem's buffer role, loaded a whole problem ahead of its use
+      fw += nwarps;
+      fb = fw < WL.n ? WL.at(fw) : 0;
+      if (sel && lane == 0 && fw < WL.n) fsel = sel[fb];        // next problem's buffer role, loaded a whole problem ahead of its use
     }
   };
 #pragma unroll
@@ -724,7 +736,8 @@ k_model_wpp(const T* __restrict__ p, const T* __restrict__ x, const T* __restric
 
   unsigned st = 0, ph = 0;
   const T w0 = (MODE == WPP_COST) ? T(1) : w[0];
-  for (long long b = wid; b < B; b += nwarps) {
+  for (long long wi = wid; wi < WL.n; wi += nwarps) {
+    const long long b = WL.at(wi);
     Model M;
     M.load(p + b * P);
     RowAcc<TA, P> acc;
@@ -940,15 +953,17 @@ __global__ void __launch_bounds__(TPB)
 k_model_normal_eq_gda(const T* __restrict__ p, const T* __restrict__ x, const T* __restrict__ y, long long ybs,
                       long long ycs, const T* __restrict__ w, int wlen, long long B, int C, int N, T* fsA, T* fsB,
                       double* __restrict__ g64, double* __restrict__ H64, double* __restrict__ stats,
-                      const nlls_ctrl* ctrl) {
+                      const nlls_ctrl* ctrl, nlls_track tr) {
   if (is_done(ctrl)) return;
   constexpr int P = Model::P, NW = TPB / 32, NH = Tri<P>::N, V = P + NH + 2;
   const int it = iter_index(ctrl);
+  const WorkList WL(tr, it, B);
   T* __restrict__ fs_out = (it & 1) ? fsB : fsA;
   const T* __restrict__ fs_prev = (it > 0 && fsA) ? ((it & 1) ? fsA : fsB) : nullptr;
   __shared__ double red[NW * V];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  for (long long b = blockIdx.x; b < B; b += gridDim.x) {
+  for (long long wi = blockIdx.x; wi < WL.n; wi += gridDim.x) {
+    const long long b = WL.at(wi);
     Model M;
     M.load(p + b * P);
     RowAcc<double, P> acc;
@@ -1071,7 +1086,7 @@ k_model_cost_stat_staged(const T* __restrict__ p, const T* __restrict__ x, const
   double* sfc = reinterpret_cast<double*>(smem_raw + Ring::bytes(Cy, 0));    // [2][C][TPB]
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   Ring R;
-  R.init(smem_raw, y, ybs, ycs, Cy, nullptr, 0, 0, 0, B, N);
+  R.init(smem_raw, y, ybs, ycs, Cy, nullptr, 0, 0, 0, WorkList(nlls_track{}, 0, B), N);
   int pbuf = 0;
   for (long long b = blockIdx.x; b < B; b += gridDim.x, pbuf ^= 1) {
     Model M;
@@ -1130,7 +1145,7 @@ k_model_cost_stat_vec(const T* __restrict__ p, const T* __restrict__ x, const T*
   double* sfc = reinterpret_cast<double*>(smem_raw + Ring::bytes(Cy, 0));    // [2][C][TPB]
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   Ring R;
-  R.init(smem_raw, y, ybs, ycs, Cy, nullptr, 0, 0, 0, B, N);
+  R.init(smem_raw, y, ybs, ycs, Cy, nullptr, 0, 0, 0, WorkList(nlls_track{}, 0, B), N);
   int pbuf = 0;
   const int ystep = (Cy == 1) ? 0 : TN;
   for (long long b = blockIdx.x; b < B; b += gridDim.x, pbuf ^= 1) {
@@ -1190,12 +1205,13 @@ __global__ void __launch_bounds__(TPB)
 k_model_normal_eq_gda_staged(const T* __restrict__ p, const T* __restrict__ x, const T* __restrict__ y, long long ybs,
                              long long ycs, const T* __restrict__ w, int wlen, long long B, int C, int N, T* fsA, T* fsB,
                              double* __restrict__ g64, double* __restrict__ H64, double* __restrict__ stats,
-                             const nlls_ctrl* ctrl) {
+                             const nlls_ctrl* ctrl, nlls_track tr) {
   if (is_done(ctrl)) return;
   constexpr int P = Model::P, NW = TPB / 32, NH = Tri<P>::N, V = P + NH + 2, TN = TPB * S;
   constexpr int VP = Pow2Ceil<V>::value, OWN = 32 / VP;
   static_assert(V <= 32, "model with too many parameters for the transposed reduction");
   const int it = iter_index(ctrl);
+  const WorkList WL(tr, it, B);
   T* __restrict__ fs_out = (it & 1) ? fsB : fsA;
   const T* __restrict__ fs_prev = (it > 0 && fsA) ? ((it & 1) ? fsA : fsB) : nullptr;
   const bool has_prev = fs_prev != nullptr;
@@ -1205,12 +1221,13 @@ k_model_normal_eq_gda_staged(const T* __restrict__ p, const T* __restrict__ x, c
   double* red = reinterpret_cast<double*>(smem_raw + Ring::bytes(Cy, 1));    // [2][NW][VP]
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   Ring R;
-  R.init(smem_raw, y, ybs, ycs, Cy, fs_prev, N, 0, 1, B, N);
+  R.init(smem_raw, y, ybs, ycs, Cy, fs_prev, N, 0, 1, WL, N);
   int pbuf = 0;
-  for (long long b = blockIdx.x; b < B; b += gridDim.x, pbuf ^= 1) {
+  for (long long wi = blockIdx.x; wi < WL.n; wi += gridDim.x, pbuf ^= 1) {
+    const long long b = WL.at(wi);
     Model M;
     M.load(p + b * P);
-    if (tid == 0 && b + gridDim.x < B) prefetch_l1(p + (b + gridDim.x) * P);
+    if (tid == 0 && wi + gridDim.x < WL.n) prefetch_l1(p + WL.at(wi + gridDim.x) * P);
     RowAcc<double, P> acc;
     acc.clear();
     double sd = 0.0, sq = 0.0;
@@ -1368,7 +1385,7 @@ __global__ void __launch_bounds__(NW * 32, MINB)
 k_model_normal_eq_mma(const T* __restrict__ p, const T* __restrict__ x, const T* __restrict__ y, long long ybs, long long ycs,
                       const T* __restrict__ w, int wlen, long long B, int C, int N, T* fA, T* fB, void* __restrict__ gout_,
                       void* __restrict__ Hout_, double* __restrict__ stats, const nlls_ctrl* ctrl,
-                      const unsigned char* __restrict__ sel) {
+                      const unsigned char* __restrict__ sel, nlls_track tr) {
   using TO = typename std::conditional<GDA, double, T>::type;
   TO* __restrict__ gout = reinterpret_cast<TO*>(gout_);
   TO* __restrict__ Hout = reinterpret_cast<TO*>(Hout_);
@@ -1383,9 +1400,11 @@ k_model_normal_eq_mma(const T* __restrict__ p, const T* __restrict__ x, const T*
   const int k = lane & 3, gi = lane >> 2;
   double* tile = tiles + warp * 32 * ROWD;
   const int it = iter_index(ctrl);
+  const WorkList WL(tr, it, B);
   const int NBATCH = (N + 31) >> 5;
 
-  for (long long b = blockIdx.x; b < B; b += gridDim.x) {
+  for (long long wi = blockIdx.x; wi < WL.n; wi += gridDim.x) {
+    const long long b = WL.at(wi);
     T* f_out = (it & 1) ? fB : fA;
     const T* f_prev = (it > 0 && fA) ? ((it & 1) ? fA : fB) : nullptr;
     if (sel) { const bool s1 = sel[b] != 0; f_out = s1 ? fA : fB; f_prev = s1 ? fB : fA; }
@@ -1546,6 +1565,7 @@ struct ModelArgs {
   double *g64, *H64, *stats, *stat_out;
   void *f_out, *J_out;
   const unsigned char* sel;          // speculative LM: per-problem current-buffer flags (NULL otherwise)
+  nlls_track tr;                     // per-problem tracking / retirement (zeroed: none)
   const nlls_ctrl* ctrl;
   cudaStream_t st;
 };
@@ -1582,7 +1602,7 @@ static int launch_staged(const ModelArgs& a) {
   auto launch = [&](auto kern2) {
     const int grid2 = grid_for(kern2, TPB2, smem2, a.B);
     kern2<<<grid2, TPB2, smem2, a.st>>>((const T*)a.p, (const T*)a.x, (const T*)a.y, a.ybs, a.ycs, (const T*)a.w, a.wlen,
-                                        a.B, a.C, a.N, (T*)a.fA, (T*)a.fB, (T*)a.g, (T*)a.H, a.stats, a.ctrl, a.sel);
+                                        a.B, a.C, a.N, (T*)a.fA, (T*)a.fB, (T*)a.g, (T*)a.H, a.stats, a.ctrl, a.sel, a.tr);
   };
   if (three) launch(k_model_normal_eq_staged<T, Model, TPB2, S2, 3, CT, MINB>);
   else launch(k_model_normal_eq_staged<T, Model, TPB2, S2, 2, CT, MINB>);
@@ -1629,7 +1649,7 @@ static int launch_vec(const ModelArgs& a) {
   auto launch = [&](auto kern2) {
     const int grid2 = grid_for(kern2, TPB2, smem2, a.B);
     kern2<<<grid2, TPB2, smem2, a.st>>>((const T*)a.p, (const T*)a.x, (const T*)a.y, a.ybs, a.ycs, (const T*)a.w, a.wlen,
-                                        a.B, a.C, a.N, (T*)a.fA, (T*)a.fB, (T*)a.g, (T*)a.H, a.stats, a.ctrl, a.sel);
+                                        a.B, a.C, a.N, (T*)a.fA, (T*)a.fB, (T*)a.g, (T*)a.H, a.stats, a.ctrl, a.sel, a.tr);
   };
   if (three) launch(k_model_normal_eq_vec<T, Model, TPB2, 3>);
   else launch(k_model_normal_eq_vec<T, Model, TPB2, 2>);
@@ -1668,7 +1688,8 @@ static int launch_wpp(const ModelArgs& a) {
   auto go = [&](auto kern) {
     const int grid = grid_for(kern, NW * 32, smem, (a.B + NW - 1) / NW);
     kern<<<grid, NW * 32, smem, a.st>>>((const T*)a.p, (const T*)a.x, (const T*)a.y, a.ybs, a.ycs, (const T*)a.w, a.wlen, a.B,
-                                        a.C, a.N, (T*)a.fA, (T*)a.fB, og, oH, os, a.ctrl, CH, MODE == WPP_NEQ ? a.sel : nullptr);
+                                        a.C, a.N, (T*)a.fA, (T*)a.fB, og, oH, os, a.ctrl, CH, MODE == WPP_NEQ ? a.sel : nullptr,
+                                        MODE == WPP_COST ? nlls_track{} : a.tr);
   };
   if (vl) go(k_model_wpp<T, Model, MODE, 16 / (int)sizeof(T), NSTAGE, NW, true, true>);
   else if (c1) go(k_model_wpp<T, Model, MODE, SB, NSTAGE, NW, true>);
@@ -1735,7 +1756,7 @@ static int launch_gda_staged(const ModelArgs& a) {
   auto launch = [&](auto kern2) {
     const int grid2 = grid_for(kern2, TPB2, smem2, a.B);
     kern2<<<grid2, TPB2, smem2, a.st>>>((const T*)a.p, (const T*)a.x, (const T*)a.y, a.ybs, a.ycs, (const T*)a.w, a.wlen, a.B,
-                                        a.C, a.N, (T*)a.fA, (T*)a.fB, a.g64, a.H64, a.stats, a.ctrl);
+                                        a.C, a.N, (T*)a.fA, (T*)a.fB, a.g64, a.H64, a.stats, a.ctrl, a.tr);
   };
   if (three) launch(k_model_normal_eq_gda_staged<T, Model, TPB2, S2, 3>);
   else launch(k_model_normal_eq_gda_staged<T, Model, TPB2, S2, 2>);
@@ -1794,7 +1815,7 @@ static int run_op(Op op, const ModelArgs& a) {
       auto kern = k_model_normal_eq<T, Model, TPB, S>;
       const int grid = grid_for(kern, TPB, smem, a.B);
       kern<<<grid, TPB, smem, a.st>>>((const T*)a.p, (const T*)a.x, (const T*)a.y, a.ybs, a.ycs, (const T*)a.w, a.wlen, a.B,
-                                      a.C, a.N, (T*)a.fA, (T*)a.fB, (T*)a.g, (T*)a.H, a.stats, a.ctrl, a.sel);
+                                      a.C, a.N, (T*)a.fA, (T*)a.fB, (T*)a.g, (T*)a.H, a.stats, a.ctrl, a.sel, a.tr);
       return check_launch("nlls_model_normal_eq");
     }
     case OP_NEQ_GDA: {
@@ -1809,7 +1830,7 @@ static int run_op(Op op, const ModelArgs& a) {
       auto kern = k_model_normal_eq_gda<T, Model, TPB>;
       const int grid = grid_for(kern, TPB, 0, a.B);
       kern<<<grid, TPB, 0, a.st>>>((const T*)a.p, (const T*)a.x, (const T*)a.y, a.ybs, a.ycs, (const T*)a.w, a.wlen, a.B, a.C,
-                                   a.N, (T*)a.fA, (T*)a.fB, a.g64, a.H64, a.stats, a.ctrl);
+                                   a.N, (T*)a.fA, (T*)a.fB, a.g64, a.H64, a.stats, a.ctrl, a.tr);
       return check_launch("nlls_model_normal_eq_gda");
     }
     case OP_COST: {
@@ -1860,7 +1881,7 @@ static int run_wide(Op op, const ModelArgs& a, const char* name) {
       const int grid = grid_for(kern, TPB, smem, a.B);
       kern<<<grid, TPB, smem, a.st>>>((const T*)a.p, (const T*)a.x, (const T*)a.y, a.ybs, a.ycs, (const T*)a.w, a.wlen, a.B,
                                       a.C, a.N, (T*)a.fA, (T*)a.fB, gda ? (void*)a.g64 : a.g, gda ? (void*)a.H64 : a.H, a.stats,
-                                      a.ctrl, a.sel);
+                                      a.ctrl, a.sel, a.tr);
       return check_launch(gda ? "nlls_model_normal_eq_gda(mma)" : "nlls_model_normal_eq(mma)");
     };
     if (gda) return go(k_model_normal_eq_mma<T, Model, 4, 6, true>, 4);
@@ -1941,8 +1962,9 @@ extern "C" int nlls_model_eval(int model, int dtype, const void* p, int P, const
 extern "C" int nlls_model_normal_eq(int model, int dtype, const void* p, int P, const void* x, const void* y,
                                     long long y_bstride, long long y_cstride, const void* wvec, int wlen, long long B, int C,
                                     int N, void* m_pp0, void* m_pp1, void* g, void* H, double* stats, const nlls_ctrl* ctrl,
-                                    void* stream) {
+                                    const nlls_track* track, void* stream) {
   ModelArgs a{};
+  a.tr = track_or_none(track);
   a.p = p; a.x = x; a.y = y; a.w = wvec; a.ybs = y_bstride; a.ycs = y_cstride; a.B = B; a.C = C; a.N = N; a.wlen = wlen;
   a.fA = m_pp0; a.fB = m_pp1; a.g = g; a.H = H; a.stats = stats; a.ctrl = ctrl; a.st = (cudaStream_t)stream;
   if (!wvec || !g || !H || !stats || (m_pp0 && !m_pp1)) { set_error("nlls_model_normal_eq: NULL tensor"); return NLLS_E_NULL; }
@@ -1952,8 +1974,9 @@ extern "C" int nlls_model_normal_eq(int model, int dtype, const void* p, int P, 
 extern "C" int nlls_model_normal_eq_gda(int model, int dtype, const void* p, int P, const void* x, const void* y,
                                         long long y_bstride, long long y_cstride, const void* wvec, int wlen, long long B,
                                         int C, int N, void* fsum_pp0, void* fsum_pp1, double* g64, double* H64, double* stats,
-                                        const nlls_ctrl* ctrl, void* stream) {
+                                        const nlls_ctrl* ctrl, const nlls_track* track, void* stream) {
   ModelArgs a{};
+  a.tr = track_or_none(track);
   a.p = p; a.x = x; a.y = y; a.w = wvec; a.ybs = y_bstride; a.ycs = y_cstride; a.B = B; a.C = C; a.N = N; a.wlen = wlen;
   a.fA = fsum_pp0; a.fB = fsum_pp1; a.g64 = g64; a.H64 = H64; a.stats = stats; a.ctrl = ctrl; a.st = (cudaStream_t)stream;
   if (!wvec || !g64 || !H64 || !stats || (fsum_pp0 && !fsum_pp1)) { set_error("nlls_model_normal_eq_gda: NULL tensor"); return NLLS_E_NULL; }
@@ -1973,8 +1996,9 @@ extern "C" int nlls_model_cost_stat(int model, int dtype, const void* p_trial, i
 extern "C" int nlls_model_lm_trial(int model, int dtype, const void* p_trial, int P, const void* x, const void* y,
                                    long long y_bstride, long long y_cstride, const void* wvec, int wlen, long long B, int C,
                                    int N, void* m_buf0, void* m_buf1, const unsigned char* sel, void* g_t, void* H_t,
-                                   double* stats_t, const nlls_ctrl* ctrl, void* stream) {
+                                   double* stats_t, const nlls_ctrl* ctrl, const nlls_track* track, void* stream) {
   ModelArgs a{};
+  a.tr = track_or_none(track);
   a.p = p_trial; a.x = x; a.y = y; a.w = wvec; a.ybs = y_bstride; a.ycs = y_cstride; a.B = B; a.C = C; a.N = N; a.wlen = wlen;
   a.fA = m_buf0; a.fB = m_buf1; a.g = g_t; a.H = H_t; a.stats = stats_t; a.sel = sel; a.ctrl = ctrl; a.st = (cudaStream_t)stream;
   if (!wvec || !g_t || !H_t || !stats_t || !m_buf0 || !m_buf1 || !sel) { set_error("nlls_model_lm_trial: NULL tensor"); return NLLS_E_NULL; }

@@ -13,6 +13,8 @@ namespace nlls {
 
 constexpr int kUpdTPB = 128;
 
+template <typename T> __device__ __forceinline__ bool not_finite(T v) { return !(fabs(v) <= (T)1.7976931348623157e308); }
+template <> __device__ __forceinline__ bool not_finite<float>(float v) { return !(fabsf(v) <= 3.4028234663852886e38f); }
 template <typename T> __device__ __forceinline__ T nan_max(T a, T b) { return (a != a) ? a : ((b != b) ? b : (a > b ? a : b)); }
 
 // ------------------------------------------------------------------- solve dispatch
@@ -111,11 +113,12 @@ __device__ __forceinline__ void gp_tests(int P, const T* gb, int gstride, const 
 template <typename T>
 __global__ void k_lm_solve(const T* __restrict__ g, const T* __restrict__ H, const T* __restrict__ p,
                            const T* __restrict__ u, T* __restrict__ dscale, int marquardt, long long B, int P,
-                           T* __restrict__ h, T* __restrict__ p_trial, nlls_ctrl* ctrl) {
+                           T* __restrict__ h, T* __restrict__ p_trial, nlls_ctrl* ctrl, nlls_track tr) {
   if (is_done(ctrl)) return;
   extern __shared__ double scratch[];
   const long long b = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (b >= B) return;
+  if (track_frozen(tr, b)) return;                   // retired problem: no solve, no damping update
   const T* Hb = H + b * P * P;
   T dd = dscale[b * 2], doff = dscale[b * 2 + 1];
   if (marquardt) {                                   // lma:88 — D <- D * max_p max(H_pp, D_pp)   (Q6)
@@ -142,12 +145,18 @@ template <typename T>
 __global__ void k_lm_update(T* __restrict__ p, const T* __restrict__ h, const T* __restrict__ g, T* __restrict__ u,
                             T* __restrict__ v, const double* __restrict__ stats, const double* __restrict__ stat_h,
                             int meth, T rho1, T rho2, T beta, T gama, double ftol, T ptol, T gtol, long long B, int P,
-                            T* __restrict__ p_hist, T* __restrict__ rho_out, nlls_ctrl* ctrl) {
+                            T* __restrict__ p_hist, T* __restrict__ rho_out, nlls_ctrl* ctrl, nlls_track tr) {
   if (is_done(ctrl)) return;
   const int it = iter_index(ctrl);
   const long long b = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   int nc_open = 0, accepted = 0, nc_closed = 0;
-  if (b < B) {
+  bool keep = false;
+  if (b < B && track_frozen(tr, b)) {                // retired: the snapshot repeats the frozen iterate
+    if (p_hist) {
+      T* snap = p_hist + ((long long)it * B + b) * P;
+      for (int i = 0; i < P; ++i) snap[i] = p[b * P + i];
+    }
+  } else if (b < B) {
     const T* hb = h + b * P;
     const T* gb = g + b * P;
     T* pb = p + b * P;
@@ -185,11 +194,19 @@ __global__ void k_lm_update(T* __restrict__ p, const T* __restrict__ h, const T*
     const bool fcon = (it > 0) && (stats[b * 4 + 1] < ftol * ftol * stats[b * 4 + 2]);   // lma:110
     nc_open = !(gcon || pcon || fcon);
     nc_closed = !(gcon || pcon);
+    if (tr.pstat) {                                  // the problem's own test: fcon only with an accepted step of its own
+      const bool own = gcon || pcon || (fcon && accepted);
+      bool bad = false;
+      for (int i = 0; i < P; ++i) bad = bad || not_finite(hb[i]);
+      track_record(tr, b, own, (gcon ? 1 : 0) | (pcon ? 2 : 0) | ((fcon && accepted) ? 4 : 0), accepted, bad, it);
+      if (tr.retire) { nc_open = nc_closed = !own; keep = !own; }
+    }
     if (p_hist) {
       T* snap = p_hist + ((long long)it * B + b) * P;
       for (int i = 0; i < P; ++i) snap[i] = pb[i];   // lma:116
     }
   }
+  if (tr.retire) track_append(tr, it, b, keep);
   if (ctrl) block_count_add(ctrl, nc_open, accepted, nc_closed);
 }
 
@@ -203,12 +220,18 @@ __global__ void k_lm_update_spec(T* __restrict__ p, const T* __restrict__ h, T* 
                                  T* __restrict__ v, double* __restrict__ stats, const double* __restrict__ stats_t,
                                  unsigned char* __restrict__ sel, int meth, T rho1, T rho2, T beta, T gama, double ftol,
                                  T ptol, T gtol, long long B, int P, T* __restrict__ p_hist, T* __restrict__ rho_out,
-                                 nlls_ctrl* ctrl) {
+                                 nlls_ctrl* ctrl, nlls_track tr) {
   if (is_done(ctrl)) return;
   const int it = iter_index(ctrl);
   const long long b = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   int nc_open = 0, accepted = 0, nc_closed = 0;
-  if (b < B) {
+  bool keep = false;
+  if (b < B && track_frozen(tr, b)) {                // retired: the snapshot repeats the frozen iterate
+    if (p_hist) {
+      T* snap = p_hist + ((long long)it * B + b) * P;
+      for (int i = 0; i < P; ++i) snap[i] = p[b * P + i];
+    }
+  } else if (b < B) {
     const T* hb = h + b * P;
     T* gb = g + b * P;
     T* pb = p + b * P;
@@ -245,6 +268,13 @@ __global__ void k_lm_update_spec(T* __restrict__ p, const T* __restrict__ h, T* 
     const bool fcon = (it > 0) && (stats[b * 4 + 1] < ftol * ftol * stats[b * 4 + 2]);
     nc_open = !(gcon || pcon || fcon);
     nc_closed = !(gcon || pcon);
+    if (tr.pstat) {                                  // the problem's own test: fcon only with an accepted step of its own
+      const bool own = gcon || pcon || (fcon && accepted);
+      bool bad = false;
+      for (int i = 0; i < P; ++i) bad = bad || not_finite(hb[i]);
+      track_record(tr, b, own, (gcon ? 1 : 0) | (pcon ? 2 : 0) | ((fcon && accepted) ? 4 : 0), accepted, bad, it);
+      if (tr.retire) { nc_open = nc_closed = !own; keep = !own; }
+    }
     if (p_hist) {
       T* snap = p_hist + ((long long)it * B + b) * P;
       for (int i = 0; i < P; ++i) snap[i] = pb[i];
@@ -262,6 +292,7 @@ __global__ void k_lm_update_spec(T* __restrict__ p, const T* __restrict__ h, T* 
       stats[b * 4 + 1] = 0.0;                        // f unchanged: sum (f_prev - f)^2 == 0 at the next fcon
     }
   }
+  if (tr.retire) track_append(tr, it, b, keep);
   if (ctrl) block_count_add(ctrl, nc_open, accepted, nc_closed);
 }
 
@@ -269,13 +300,19 @@ __global__ void k_lm_update_spec(T* __restrict__ p, const T* __restrict__ h, T* 
 template <typename T>
 __global__ void k_gn_update(T* __restrict__ p, const T* __restrict__ g, const T* __restrict__ H,
                             const double* __restrict__ stats, T l, double ftol, T ptol, T gtol, int with_masks,
-                            long long B, int P, T* __restrict__ h_out, T* __restrict__ p_hist, nlls_ctrl* ctrl) {
+                            long long B, int P, T* __restrict__ h_out, T* __restrict__ p_hist, nlls_ctrl* ctrl, nlls_track tr) {
   if (is_done(ctrl)) return;
   extern __shared__ double scratch[];
   const int it = iter_index(ctrl);
   const long long b = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   int nc = 0;
-  if (b < B) {
+  bool keep = false;
+  if (b < B && track_frozen(tr, b)) {                // retired: the snapshot repeats the frozen iterate
+    if (p_hist) {
+      T* snap = p_hist + ((long long)it * B + b) * P;
+      for (int i = 0; i < P; ++i) snap[i] = p[b * P + i];
+    }
+  } else if (b < B) {
     double x[NLLS_MAX_P];
     const bool ok = solve_any<T, T>(P, H + b * P * P, g + b * P, T(0), T(0), false, x, scratch + threadIdx.x, blockDim.x);
     if (!ok && ctrl) ctrl->singular = 1;             // gna:74-75 warns on an infinite condition number
@@ -291,26 +328,39 @@ __global__ void k_gn_update(T* __restrict__ p, const T* __restrict__ g, const T*
       gp_tests<T>(P, g + b * P, 1, hb, pb, gtol, ptol, gcon, pcon);
       const bool fcon = (it > 0) && (stats[b * 4 + 1] < ftol * ftol * stats[b * 4 + 2]);   // gna:80
       nc = !(gcon || pcon || fcon);
+      if (tr.pstat) {
+        bool bad = false;
+        for (int i = 0; i < P; ++i) bad = bad || not_finite(hb[i]);
+        track_record(tr, b, !nc, (gcon ? 1 : 0) | (pcon ? 2 : 0) | (fcon ? 4 : 0), 1, bad, it);
+        keep = tr.retire && nc;
+      }
     }
     if (p_hist) {
       T* snap = p_hist + ((long long)it * B + b) * P;
       for (int i = 0; i < P; ++i) snap[i] = pb[i];   // gna:86
     }
   }
+  if (tr.retire) track_append(tr, it, b, keep);
   if (ctrl && with_masks) block_count_add(ctrl, nc, 0, 0);
 }
 
 // ---------------------------------------------------------------------------- GD update
 template <typename T>
-__global__ void k_gd_update(T* __restrict__ p, const double* __restrict__ g64, const double* __restrict__ H64, T l,
-                            T ptol, T gtol, int with_masks, long long B, int P, T* __restrict__ h_out,
-                            T* __restrict__ p_hist, nlls_ctrl* ctrl) {
+__global__ void k_gd_update(T* __restrict__ p, const double* __restrict__ g64, const double* __restrict__ H64,
+                            const double* __restrict__ stats, T l, double ftol, T ptol, T gtol, int with_masks, long long B,
+                            int P, T* __restrict__ h_out, T* __restrict__ p_hist, nlls_ctrl* ctrl, nlls_track tr) {
   if (is_done(ctrl)) return;
   extern __shared__ double scratch[];
   const int it = iter_index(ctrl);
   const long long b = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   int nc = 0;
-  if (b < B) {
+  bool keep = false;
+  if (b < B && track_frozen(tr, b)) {                // retired: the snapshot repeats the frozen iterate
+    if (p_hist) {
+      T* snap = p_hist + ((long long)it * B + b) * P;
+      for (int i = 0; i < P; ++i) snap[i] = p[b * P + i];
+    }
+  } else if (b < B) {
     double x[NLLS_MAX_P];
     const bool ok = solve_any<double, double>(P, H64 + b * P * P, g64 + b * P, 0.0, 0.0, false, x, scratch + threadIdx.x, blockDim.x);
     if (!ok && ctrl) ctrl->singular = 1;
@@ -326,12 +376,21 @@ __global__ void k_gd_update(T* __restrict__ p, const double* __restrict__ g64, c
       bool gcon, pcon;
       gp_tests<T>(P, gb, 1, hb, pb, gtol, ptol, gcon, pcon);
       nc = !(gcon || pcon);
+      if (tr.pstat) {                                // own test: fcon on the problem's own sums (gda:76 sums over the batch)
+        const bool fcon = (it > 0) && (stats[b * 4 + 1] < ftol * ftol * stats[b * 4 + 2]);
+        const bool own = gcon || pcon || fcon;
+        bool bad = false;
+        for (int i = 0; i < P; ++i) bad = bad || not_finite(hb[i]);
+        track_record(tr, b, own, (gcon ? 1 : 0) | (pcon ? 2 : 0) | (fcon ? 4 : 0), 1, bad, it);
+        if (tr.retire) { nc = !own; keep = !own; }
+      }
     }
     if (p_hist) {
       T* snap = p_hist + ((long long)it * B + b) * P;
       for (int i = 0; i < P; ++i) snap[i] = pb[i];
     }
   }
+  if (tr.retire) track_append(tr, it, b, keep);
   if (ctrl && with_masks) block_count_add(ctrl, nc, 0, 0);
 }
 
@@ -352,9 +411,10 @@ __global__ void __launch_bounds__(1024) k_reduce_stats(const double* __restrict_
   if (threadIdx.x == 0) { ctrl->red[2] += s1[0]; ctrl->red[3] += s2[0]; }
 }
 
-__global__ void k_iter_end(nlls_ctrl* ctrl, int solver, double ftol) {
+__global__ void k_iter_end(nlls_ctrl* ctrl, int solver, double ftol, nlls_track tr) {
   if (ctrl->done) return;
   const int it = ctrl->iters;
+  if (tr.retire) tr.count[it & 1] = 0;               // this iteration's list is consumed; it is the one after next's append target
   bool done;
   if (solver == NLLS_SOLVER_LM) {
     const bool gate = ctrl->red[1] > 0.0;            // (rho > 0).sum() > 0  (lma:110, Q10)
@@ -535,6 +595,7 @@ struct WideArgs {
   long long B;
   int P, marquardt, with_masks;
   nlls_ctrl* ctrl;
+  nlls_track tr;
 };
 constexpr int kWideWarps = 4;
 template <int PP> constexpr size_t wide_smem_bytes() { return (size_t)kWideWarps * (2 * PP * (PP + 1) + 2 * PP) * 8; }
@@ -562,6 +623,10 @@ __global__ void __launch_bounds__(kWideWarps * 32) k_solve_wide(WideArgs a) {
   T* p = reinterpret_cast<T*>(a.p);
   int nc = 0, sing = 0;
   for (long long b = (long long)blockIdx.x * kWideWarps + warp; b < a.B; b += (long long)gridDim.x * kWideWarps) {
+    if (track_frozen(a.tr, b)) {                     // retired problem (warp-uniform): only its snapshot repeats
+      if (MODE != W_LM && act && a.p_hist) reinterpret_cast<T*>(a.p_hist)[((long long)it * a.B + b) * P + lane] = p[b * P + lane];
+      continue;
+    }
     const TH* Hb = reinterpret_cast<const TH*>(a.H) + b * P * P;
     T diag_add = T(0), off_add = T(0);
     if constexpr (MODE == W_LM) {
@@ -633,7 +698,18 @@ __global__ void __launch_bounds__(kWideWarps * 32) k_solve_wide(WideArgs a) {
         const bool pcon = sqrt(hh) < (T)a.ptol * ((T)a.ptol + sqrt(pp));
         bool fcon = false;
         if constexpr (MODE == W_GN) fcon = (it > 0) && (a.stats[b * 4 + 1] < a.ftol * a.ftol * a.stats[b * 4 + 2]);
-        nc += !(gcon || pcon || fcon);
+        bool conv = gcon || pcon || fcon;
+        if (a.tr.pstat) {                            // the problem's own test (GD: fcon on its own sums, gda:76 sums the batch)
+          const bool fown = (MODE == W_GD) ? ((it > 0) && (a.stats[b * 4 + 1] < a.ftol * a.ftol * a.stats[b * 4 + 2])) : fcon;
+          const bool own = gcon || pcon || fown;
+          const bool bad = __any_sync(0xffffffffu, not_finite(hb));
+          if (lane == 0) {
+            track_record(a.tr, b, own, (gcon ? 1 : 0) | (pcon ? 2 : 0) | (fown ? 4 : 0), 1, bad, it);
+            if (a.tr.retire && !own) a.tr.active[(size_t)((it + 1) & 1) * a.tr.B + atomicAdd(a.tr.count + ((it + 1) & 1), 1)] = (int)b;
+          }
+          if (a.tr.retire) conv = own;
+        }
+        nc += !conv;
       }
     }
   }
@@ -676,14 +752,16 @@ static int check_bp(int dtype, long long B, int P) {
 }
 
 extern "C" int nlls_lm_solve(int dtype, const void* g, const void* H, const void* p, const void* u, void* dscale,
-                             int marquardt, long long B, int P, void* h, void* p_trial, nlls_ctrl* ctrl, void* stream) {
+                             int marquardt, long long B, int P, void* h, void* p_trial, nlls_ctrl* ctrl, const nlls_track* track,
+                             void* stream) {
+  const nlls_track tr = track_or_none(track);
   if (int e = check_bp(dtype, B, P)) return e;
   if (B == 0) return 0;
   if (!g || !H || !p || !u || !dscale || !h || !p_trial) { set_error("nlls_lm_solve: NULL tensor"); return NLLS_E_NULL; }
   if (P > 8 && !g_force_direct) {
     WideArgs a{};
     a.g = g; a.H = H; a.u = u; a.p = const_cast<void*>(p); a.dscale = dscale; a.h = h; a.p_trial = p_trial;
-    a.B = B; a.P = P; a.marquardt = marquardt; a.ctrl = ctrl;
+    a.B = B; a.P = P; a.marquardt = marquardt; a.ctrl = ctrl; a.tr = tr;
     return dtype == NLLS_F64 ? launch_wide<double, W_LM>(a, (cudaStream_t)stream, "nlls_lm_solve(wide)")
                              : launch_wide<float, W_LM>(a, (cudaStream_t)stream, "nlls_lm_solve(wide)");
   }
@@ -694,11 +772,11 @@ extern "C" int nlls_lm_solve(int dtype, const void* g, const void* H, const void
   if (dtype == NLLS_F64) {
     allow_smem(k_lm_solve<double>, smem);
     k_lm_solve<double><<<grid, tpb, smem, st>>>((const double*)g, (const double*)H, (const double*)p, (const double*)u,
-                                                (double*)dscale, marquardt, B, P, (double*)h, (double*)p_trial, ctrl);
+                                                (double*)dscale, marquardt, B, P, (double*)h, (double*)p_trial, ctrl, tr);
   } else {
     allow_smem(k_lm_solve<float>, smem);
     k_lm_solve<float><<<grid, tpb, smem, st>>>((const float*)g, (const float*)H, (const float*)p, (const float*)u,
-                                               (float*)dscale, marquardt, B, P, (float*)h, (float*)p_trial, ctrl);
+                                               (float*)dscale, marquardt, B, P, (float*)h, (float*)p_trial, ctrl, tr);
   }
   return check_launch("nlls_lm_solve");
 }
@@ -706,7 +784,8 @@ extern "C" int nlls_lm_solve(int dtype, const void* g, const void* H, const void
 extern "C" int nlls_lm_update(int dtype, void* p, const void* h, const void* g, void* u, void* v, const double* stats,
                               const double* stat_h, int meth, double rho1, double rho2, double beta, double gama,
                               double ftol, double ptol, double gtol, long long B, int P, void* p_hist, void* rho_out,
-                              nlls_ctrl* ctrl, void* stream) {
+                              nlls_ctrl* ctrl, const nlls_track* track, void* stream) {
+  const nlls_track tr = track_or_none(track);
   if (int e = check_bp(dtype, B, P)) return e;
   if (B == 0) return 0;
   if (!p || !h || !g || !u || !v || !stats || !stat_h) { set_error("nlls_lm_update: NULL tensor"); return NLLS_E_NULL; }
@@ -715,24 +794,25 @@ extern "C" int nlls_lm_update(int dtype, void* p, const void* h, const void* g, 
   if (dtype == NLLS_F64)
     k_lm_update<double><<<grid, kUpdTPB, 0, st>>>((double*)p, (const double*)h, (const double*)g, (double*)u, (double*)v,
                                                   stats, stat_h, meth, rho1, rho2, beta, gama, ftol, ptol, gtol, B, P,
-                                                  (double*)p_hist, (double*)rho_out, ctrl);
+                                                  (double*)p_hist, (double*)rho_out, ctrl, tr);
   else
     k_lm_update<float><<<grid, kUpdTPB, 0, st>>>((float*)p, (const float*)h, (const float*)g, (float*)u, (float*)v, stats,
                                                  stat_h, meth, (float)rho1, (float)rho2, (float)beta, (float)gama, ftol,
-                                                 (float)ptol, (float)gtol, B, P, (float*)p_hist, (float*)rho_out, ctrl);
+                                                 (float)ptol, (float)gtol, B, P, (float*)p_hist, (float*)rho_out, ctrl, tr);
   return check_launch("nlls_lm_update");
 }
 
 extern "C" int nlls_gn_update(int dtype, void* p, const void* g, const void* H, const double* stats, double l, double ftol,
                               double ptol, double gtol, int with_masks, long long B, int P, void* h_out, void* p_hist,
-                              nlls_ctrl* ctrl, void* stream) {
+                              nlls_ctrl* ctrl, const nlls_track* track, void* stream) {
+  const nlls_track tr = track_or_none(track);
   if (int e = check_bp(dtype, B, P)) return e;
   if (B == 0) return 0;
   if (!p || !g || !H || (with_masks && !stats)) { set_error("nlls_gn_update: NULL tensor"); return NLLS_E_NULL; }
   if (P > 8 && !g_force_direct) {
     WideArgs a{};
     a.g = g; a.H = H; a.p = p; a.h_out = h_out; a.p_hist = p_hist; a.stats = stats; a.l = l; a.ftol = ftol; a.ptol = ptol;
-    a.gtol = gtol; a.B = B; a.P = P; a.with_masks = with_masks && ctrl; a.ctrl = ctrl;
+    a.gtol = gtol; a.B = B; a.P = P; a.with_masks = with_masks && ctrl; a.ctrl = ctrl; a.tr = tr;
     return dtype == NLLS_F64 ? launch_wide<double, W_GN>(a, (cudaStream_t)stream, "nlls_gn_update(wide)")
                              : launch_wide<float, W_GN>(a, (cudaStream_t)stream, "nlls_gn_update(wide)");
   }
@@ -743,20 +823,20 @@ extern "C" int nlls_gn_update(int dtype, void* p, const void* g, const void* H, 
   if (dtype == NLLS_F64) {
     allow_smem(k_gn_update<double>, smem);
     k_gn_update<double><<<grid, tpb, smem, st>>>((double*)p, (const double*)g, (const double*)H, stats, l, ftol, ptol, gtol,
-                                                 with_masks, B, P, (double*)h_out, (double*)p_hist, ctrl);
+                                                 with_masks, B, P, (double*)h_out, (double*)p_hist, ctrl, tr);
   } else {
     allow_smem(k_gn_update<float>, smem);
     k_gn_update<float><<<grid, tpb, smem, st>>>((float*)p, (const float*)g, (const float*)H, stats, (float)l, ftol,
                                                 (float)ptol, (float)gtol, with_masks, B, P, (float*)h_out, (float*)p_hist,
-                                                ctrl);
+                                                ctrl, tr);
   }
   return check_launch("nlls_gn_update");
 }
 
 extern "C" int nlls_gd_update(int dtype, void* p, const double* g64, const double* H64, const double* stats, double l,
                               double ftol, double ptol, double gtol, int with_masks, long long B, int P, void* h_out,
-                              void* p_hist, nlls_ctrl* ctrl, void* stream) {
-  (void)ftol;
+                              void* p_hist, nlls_ctrl* ctrl, const nlls_track* track, void* stream) {
+  const nlls_track tr = track_or_none(track);
   if (int e = check_bp(dtype, B, P)) return e;
   if (B == 0) return 0;
   if (!p || !g64 || !H64 || (with_masks && (!stats || !ctrl))) { set_error("nlls_gd_update: NULL tensor"); return NLLS_E_NULL; }
@@ -767,20 +847,20 @@ extern "C" int nlls_gd_update(int dtype, void* p, const double* g64, const doubl
   if (P > 8 && !g_force_direct) {
     WideArgs a{};
     a.g = g64; a.H = H64; a.p = p; a.h_out = h_out; a.p_hist = p_hist; a.stats = stats; a.l = l; a.ftol = ftol; a.ptol = ptol;
-    a.gtol = gtol; a.B = B; a.P = P; a.with_masks = with_masks; a.ctrl = ctrl;
+    a.gtol = gtol; a.B = B; a.P = P; a.with_masks = with_masks; a.ctrl = ctrl; a.tr = tr;
     if (int e = dtype == NLLS_F64 ? launch_wide<double, W_GD>(a, st, "nlls_gd_update(wide)")
                                   : launch_wide<float, W_GD>(a, st, "nlls_gd_update(wide)")) return e;
   } else if (dtype == NLLS_F64) {
     allow_smem(k_gd_update<double>, smem);
-    k_gd_update<double><<<grid, tpb, smem, st>>>((double*)p, g64, H64, l, ptol, gtol, with_masks, B, P, (double*)h_out,
-                                                 (double*)p_hist, ctrl);
+    k_gd_update<double><<<grid, tpb, smem, st>>>((double*)p, g64, H64, stats, l, ftol, ptol, gtol, with_masks, B, P, (double*)h_out,
+                                                 (double*)p_hist, ctrl, tr);
   } else {
     allow_smem(k_gd_update<float>, smem);
-    k_gd_update<float><<<grid, tpb, smem, st>>>((float*)p, g64, H64, (float)l, (float)ptol, (float)gtol, with_masks, B, P,
-                                                (float*)h_out, (float*)p_hist, ctrl);
+    k_gd_update<float><<<grid, tpb, smem, st>>>((float*)p, g64, H64, stats, (float)l, ftol, (float)ptol, (float)gtol, with_masks, B, P,
+                                                (float*)h_out, (float*)p_hist, ctrl, tr);
   }
   if (int e = check_launch("nlls_gd_update")) return e;
-  if (with_masks) {
+  if (with_masks && !tr.retire) {                   // retire mode: fcon is per problem (k_gd_update), no batch sums
     k_reduce_stats<<<1, 1024, 0, st>>>(stats, B, ctrl);
     return check_launch("nlls_gd_update(reduce)");
   }
@@ -827,9 +907,9 @@ extern "C" int nlls_sumsq(int dtype, const void* a, const void* b, long long n, 
   return check_launch("nlls_sumsq");
 }
 
-extern "C" int nlls_iter_end(nlls_ctrl* ctrl, int solver, double ftol, void* stream) {
+extern "C" int nlls_iter_end(nlls_ctrl* ctrl, int solver, double ftol, const nlls_track* track, void* stream) {
   if (!ctrl) { set_error("nlls_iter_end: NULL ctrl"); return NLLS_E_NULL; }
-  k_iter_end<<<1, 1, 0, (cudaStream_t)stream>>>(ctrl, solver, ftol);
+  k_iter_end<<<1, 1, 0, (cudaStream_t)stream>>>(ctrl, solver, ftol, track_or_none(track));
   return check_launch("nlls_iter_end");
 }
 
@@ -846,7 +926,9 @@ extern "C" int nlls_iter_end_peer(nlls_ctrl* ctrl, int solver, double ftol, void
 extern "C" int nlls_lm_update_spec(int dtype, void* p, const void* h, void* g, void* H, const void* g_t, const void* H_t,
                                    void* u, void* v, double* stats, const double* stats_t, unsigned char* sel, int meth,
                                    double rho1, double rho2, double beta, double gama, double ftol, double ptol, double gtol,
-                                   long long B, int P, void* p_hist, void* rho_out, nlls_ctrl* ctrl, void* stream) {
+                                   long long B, int P, void* p_hist, void* rho_out, nlls_ctrl* ctrl, const nlls_track* track,
+                                   void* stream) {
+  const nlls_track tr = track_or_none(track);
   if (int e = check_bp(dtype, B, P)) return e;
   if (B == 0) return 0;
   if (!p || !h || !g || !H || !g_t || !H_t || !u || !v || !stats || !stats_t || !sel) {
@@ -858,11 +940,11 @@ extern "C" int nlls_lm_update_spec(int dtype, void* p, const void* h, void* g, v
     k_lm_update_spec<double><<<grid, kUpdTPB, 0, st>>>((double*)p, (const double*)h, (double*)g, (double*)H, (const double*)g_t,
                                                        (const double*)H_t, (double*)u, (double*)v, stats, stats_t, sel, meth,
                                                        rho1, rho2, beta, gama, ftol, ptol, gtol, B, P, (double*)p_hist,
-                                                       (double*)rho_out, ctrl);
+                                                       (double*)rho_out, ctrl, tr);
   else
     k_lm_update_spec<float><<<grid, kUpdTPB, 0, st>>>((float*)p, (const float*)h, (float*)g, (float*)H, (const float*)g_t,
                                                       (const float*)H_t, (float*)u, (float*)v, stats, stats_t, sel, meth,
                                                       (float)rho1, (float)rho2, (float)beta, (float)gama, ftol, (float)ptol,
-                                                      (float)gtol, B, P, (float*)p_hist, (float*)rho_out, ctrl);
+                                                      (float)gtol, B, P, (float*)p_hist, (float*)rho_out, ctrl, tr);
   return check_launch("nlls_lm_update_spec");
 }

@@ -170,18 +170,34 @@ def _check_p(p):
     _lib.dtype_code(p)
 
 
+STOP_G, STOP_P, STOP_F = 1, 2, 4        # bits of stats['stop_reason']
+
+
 @_lib.on_device_of(1)
 def solve(solver, p, function, jac_function, args, wvec, ftol, ptol, gtol, max_iter, l=1.,
-          lm=None, fused=True, check_every=_GROUP, reduce_hook=None):
+          lm=None, fused=True, check_every=_GROUP, reduce_hook=None, mode='exact', stats=None):
     """Runs one batched solve; returns the list of per-iteration snapshots (coeffs_list).
+    mode  'exact' (default): the reference's semantics — nothing freezes, the batch stops when every problem passes a stop
+          test in the same iteration.  'retire' (not in the reference; north_star kernel 3): a problem whose
+          OWN stop test fired is frozen at that iterate and never evaluated again (no host round-trip: the kernels walk a
+          device-resident list of active problems); the solve ends when no problem is left.  Its iterate equals the
+          snapshot of that iteration of an 'exact' run bit for bit; later snapshots repeat it.
+    stats optional dict, filled at return: iterations, stop_iteration [B] (first iteration at which the problem's own test
+          fired, -1 = never), stop_reason [B] (bits STOP_G | STOP_P | STOP_F at that iteration), steps [B] (LM: accepted
+          steps; GN / GD: steps taken), nonfinite [B] (a non-finite step was produced), mode.
     reduce_hook(red) — optional, multi-GPU 'exact' mode: called between the update kernel and
     nlls_iter_end with the 4 fp64 batch-global sums of the control block (a device tensor view)
     so that a caller can all-reduce(SUM) them over the ranks (torchimize_b200/sharding.py)."""
     _check_p(p)
     if p.shape[0] == 0 or max_iter <= 0:
         return []
+    if mode not in ('exact', 'retire'):
+        raise ValueError("mode must be 'exact' or 'retire'")
     if reduce_hook is None:
         reduce_hook = _default_reduce_hook
+    if mode == 'retire' and reduce_hook is not None:
+        raise _lib.NllsError("mode='retire' stops every problem on its own test: it has no batch-global decision to exchange "
+                             "between ranks (use sharding mode='local')")
     if getattr(reduce_hook, 'peer', None) is not None:
         reduce_hook.peer.epoch += 1                          # one epoch per solve, in step on every rank
     work_p = p if p.is_contiguous() else p.contiguous()
@@ -193,6 +209,16 @@ def solve(solver, p, function, jac_function, args, wvec, ftol, ptol, gtol, max_i
     B, P, code = ws.B, ws.P, ws.code
     ctrl = _lib.ptr(ws.ctrl)
     state = lm.get('state') if solver == LM else None
+    trk = None
+    if mode == 'retire' or stats is not None:               # per-problem tracking (nlls_track): device arrays, host struct
+        ws.pstat = torch.zeros(B, 4, dtype=torch.int32, device=ws.device)
+        ws.pstat[:, 0] = -1
+        trk = _lib.Track(pstat=_lib.ptr(ws.pstat), active=None, count=None, retire=0, reserved=0, B=B)
+        if mode == 'retire':
+            ws.active = torch.empty(2, B, dtype=torch.int32, device=ws.device)
+            ws.active[0] = torch.arange(B, dtype=torch.int32, device=ws.device)
+            ws.act_count = torch.tensor([B, 0], dtype=torch.int32, device=ws.device)
+            trk.active, trk.count, trk.retire = _lib.ptr(ws.active), _lib.ptr(ws.act_count), 1
     if solver == LM:
         meth = _lib.LM_LEVENBERG if lm['meth'] == 'lev' else _lib.LM_MARQUARDT
         if state:                                # warm restart: the damping state of a previous call
@@ -212,14 +238,14 @@ def solve(solver, p, function, jac_function, args, wvec, ftol, ptol, gtol, max_i
     def update(k_hist_ptr):
         if solver == GN:
             _lib.call('nlls_gn_update', code, _lib.ptr(work_p), _lib.ptr(ws.g), _lib.ptr(ws.H), _lib.ptr(ws.stats),
-                      float(l), ftol, ptol, gtol, 1, B, P, None, k_hist_ptr, ctrl, st())
+                      float(l), ftol, ptol, gtol, 1, B, P, None, k_hist_ptr, ctrl, st(), track=trk)
         elif solver == GD:
             _lib.call('nlls_gd_update', code, _lib.ptr(work_p), _lib.ptr(ws.g), _lib.ptr(ws.H), _lib.ptr(ws.stats),
-                      float(l), ftol, ptol, gtol, 1, B, P, None, k_hist_ptr, ctrl, st())
+                      float(l), ftol, ptol, gtol, 1, B, P, None, k_hist_ptr, ctrl, st(), track=trk)
         else:
             _lib.call('nlls_lm_update', code, _lib.ptr(work_p), _lib.ptr(ws.h), _lib.ptr(ws.g), _lib.ptr(ws.u),
                       _lib.ptr(ws.v), _lib.ptr(ws.stats), _lib.ptr(ws.stat_h), meth, float(lm['rho1']), float(lm['rho2']),
-                      float(lm['beta']), float(lm['gama']), ftol, ptol, gtol, B, P, k_hist_ptr, None, ctrl, st())
+                      float(lm['beta']), float(lm['gama']), ftol, ptol, gtol, B, P, k_hist_ptr, None, ctrl, st(), track=trk)
         iter_end()
 
     def iter_end():
@@ -231,11 +257,11 @@ def solve(solver, p, function, jac_function, args, wvec, ftol, ptol, gtol, max_i
             return
         if reduce_hook is not None:
             reduce_hook(ws.ctrl[2:6])
-        _lib.call('nlls_iter_end', ctrl, solver, ftol, st())
+        _lib.call('nlls_iter_end', ctrl, solver, ftol, st(), track=trk)
 
     def lm_solve():
         _lib.call('nlls_lm_solve', code, _lib.ptr(ws.g), _lib.ptr(ws.H), _lib.ptr(work_p), _lib.ptr(ws.u),
-                  _lib.ptr(ws.dscale), int(meth == _lib.LM_MARQUARDT), B, P, _lib.ptr(ws.h), _lib.ptr(ws.p_trial), ctrl, st())
+                  _lib.ptr(ws.dscale), int(meth == _lib.LM_MARQUARDT), B, P, _lib.ptr(ws.h), _lib.ptr(ws.p_trial), ctrl, st(), track=trk)
 
     if model is not None:
         # ------------------------------------------------------------------ fused path
@@ -254,7 +280,7 @@ def solve(solver, p, function, jac_function, args, wvec, ftol, ptol, gtol, max_i
             sel = torch.zeros(B, dtype=torch.uint8, device=ws.device)
             _lib.call('nlls_model_normal_eq', mid, code, _lib.ptr(work_p), P, _lib.ptr(x), _lib.ptr(y), ybs, ycs,
                       _lib.ptr(ws.w), ws.w.numel(), B, C, N, _lib.ptr(fpp[0]), _lib.ptr(fpp[1]), _lib.ptr(ws.g),
-                      _lib.ptr(ws.H), _lib.ptr(ws.stats), ctrl, st(), lib=model.lib)             # iteration 0: m(p0) -> fpp[0], sel == 0
+                      _lib.ptr(ws.H), _lib.ptr(ws.stats), ctrl, st(), lib=model.lib, track=trk)             # iteration 0: m(p0) -> fpp[0], sel == 0
         while spec and launched < max_iter and not done:
             hp = ws.hist_base_ptr(launched, max_iter)
             group = min(check_every, max_iter - launched, ws.hist_room(launched))
@@ -262,11 +288,11 @@ def solve(solver, p, function, jac_function, args, wvec, ftol, ptol, gtol, max_i
                 lm_solve()
                 _lib.call('nlls_model_lm_trial', mid, code, _lib.ptr(ws.p_trial), P, _lib.ptr(x), _lib.ptr(y), ybs, ycs,
                           _lib.ptr(ws.w), ws.w.numel(), B, C, N, _lib.ptr(fpp[0]), _lib.ptr(fpp[1]), _lib.ptr(sel),
-                          _lib.ptr(g_t), _lib.ptr(H_t), _lib.ptr(stats_t), ctrl, st(), lib=model.lib)
+                          _lib.ptr(g_t), _lib.ptr(H_t), _lib.ptr(stats_t), ctrl, st(), lib=model.lib, track=trk)
                 _lib.call('nlls_lm_update_spec', code, _lib.ptr(work_p), _lib.ptr(ws.h), _lib.ptr(ws.g), _lib.ptr(ws.H),
                           _lib.ptr(g_t), _lib.ptr(H_t), _lib.ptr(ws.u), _lib.ptr(ws.v), _lib.ptr(ws.stats), _lib.ptr(stats_t),
                           _lib.ptr(sel), meth, float(lm['rho1']), float(lm['rho2']), float(lm['beta']), float(lm['gama']),
-                          ftol, ptol, gtol, B, P, hp, None, ctrl, st())
+                          ftol, ptol, gtol, B, P, hp, None, ctrl, st(), track=trk)
                 iter_end()
             launched += group
             ws.post_flags()
@@ -278,11 +304,11 @@ def solve(solver, p, function, jac_function, args, wvec, ftol, ptol, gtol, max_i
                 if solver == GD:
                     _lib.call('nlls_model_normal_eq_gda', mid, code, _lib.ptr(work_p), P, _lib.ptr(x), _lib.ptr(y), ybs, ycs,
                               _lib.ptr(ws.w), ws.w.numel(), B, C, N, _lib.ptr(fpp[0]), _lib.ptr(fpp[1]), _lib.ptr(ws.g),
-                              _lib.ptr(ws.H), _lib.ptr(ws.stats), ctrl, st(), lib=model.lib)
+                              _lib.ptr(ws.H), _lib.ptr(ws.stats), ctrl, st(), lib=model.lib, track=trk)
                 else:
                     _lib.call('nlls_model_normal_eq', mid, code, _lib.ptr(work_p), P, _lib.ptr(x), _lib.ptr(y), ybs, ycs,
                               _lib.ptr(ws.w), ws.w.numel(), B, C, N, _lib.ptr(fpp[0]), _lib.ptr(fpp[1]), _lib.ptr(ws.g),
-                              _lib.ptr(ws.H), _lib.ptr(ws.stats), ctrl, st(), lib=model.lib)
+                              _lib.ptr(ws.H), _lib.ptr(ws.stats), ctrl, st(), lib=model.lib, track=trk)
                 if solver == LM:
                     lm_solve()
                     _lib.call('nlls_model_cost_stat', mid, code, _lib.ptr(ws.p_trial), P, _lib.ptr(x), _lib.ptr(y), ybs, ycs,
@@ -337,6 +363,9 @@ def solve(solver, p, function, jac_function, args, wvec, ftol, ptol, gtol, max_i
         p.copy_(work_p)                                     # Q1: the caller's tensor ends as the final iterate
     if state is not None:                                   # caller-owned dict, updated in place like p
         state.update(u=ws.u.clone(), v=ws.v.clone(), dscale=ws.dscale.clone(), meth=lm['meth'], iterations=int(iters))
+    if stats is not None:                                   # caller-owned dict
+        stats.update(iterations=int(iters), mode=mode, stop_iteration=ws.pstat[:, 0].clone(), stop_reason=ws.pstat[:, 1].clone(),
+                     steps=ws.pstat[:, 2].clone(), nonfinite=(ws.pstat[:, 3] & 1).bool())
     return ws.snapshots(iters)
 
 

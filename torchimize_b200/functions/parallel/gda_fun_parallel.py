@@ -17,13 +17,18 @@ def gradient_descent_parallel(
         gtol: float = 1e-8,
         l: float = 1.,
         max_iter: int = 100,
-        *, fused: bool = True,
+        *, fused: bool = True, mode: str = 'exact', stats: dict = None,
 ) -> List[torch.Tensor]:
     """The reference's "gradient descent": h = argmin || (sum_c w_c J_c) h - sum_c w_c f_c ||,
     p -= l h (gda:116-148).  The tall N x P least-squares problem is solved through fp64 normal
     equations formed in-stream (nlls_normal_eq_gda).  The f-tolerance test is one scalar for the
-    whole batch, as in the reference (gda:76)."""
-    return _engine.solve(_engine.GD, p, function, jac_function, args, wvec, ftol, ptol, gtol, max_iter, l=l, fused=fused)
+    whole batch, as in the reference (gda:76); mode='retire' tests each problem's own two sums instead.
+    Keyword-only, not in the reference: ``fused`` (in-kernel model evaluation for FusedModel callables), ``mode``
+    ('exact' = the reference's semantics; 'retire' = a problem whose own stop test fired is frozen at that iterate and never
+    evaluated again, the solve ends when none is left — see _engine.solve), ``stats`` (a caller-owned dict that receives
+    per-problem stop iteration / reason bits / step counts / non-finite flags)."""
+    return _engine.solve(_engine.GD, p, function, jac_function, args, wvec, ftol, ptol, gtol, max_iter, l=l, fused=fused,
+                         mode=mode, stats=stats)
 
 
 def gradient_descent_parallel_plain(

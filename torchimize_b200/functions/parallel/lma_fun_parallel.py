@@ -22,7 +22,7 @@ def lsq_lma_parallel(
         beta: float = 2,
         gama: float = 3,
         max_iter: int = 100,
-        *, fused: bool = True, state: dict = None,
+        *, fused: bool = True, state: dict = None, mode: str = 'exact', stats: dict = None,
 ) -> List[torch.Tensor]:
     """Batched Levenberg-Marquardt on the B200 core.
 
@@ -34,6 +34,9 @@ def lsq_lma_parallel(
     ``state`` (keyword-only, not in the reference): a caller-owned dict for warm restarts. An empty dict
     starts as the reference does (u = tau, v = 2) and receives the damping state (u, v, Marquardt scale) at return;
     passing it to the next call continues from that state, so that k calls of max_iter = n walk the same iterates as one
-    call of max_iter = k n (as long as no call stopped early)."""
+    call of max_iter = k n (as long as no call stopped early).
+    ``mode`` / ``stats`` (keyword-only, not in the reference): see _engine.solve — 'retire' freezes a problem at the iterate
+    at which its own stop test fired (fcon counts only in an iteration whose step that problem accepted)."""
     return _engine.solve(_engine.LM, p, function, jac_function, args, wvec, ftol, ptol, gtol, max_iter,
-                         lm=dict(tau=tau, meth=meth, rho1=rho1, rho2=rho2, beta=beta, gama=gama, state=state), fused=fused)
+                         lm=dict(tau=tau, meth=meth, rho1=rho1, rho2=rho2, beta=beta, gama=gama, state=state), fused=fused,
+                         mode=mode, stats=stats)

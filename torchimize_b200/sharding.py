@@ -94,10 +94,14 @@ def solve_sharded(solver_fn, p_local, function, jac_function=None, args=(), wvec
 
     solver_fn: lsq_lma_parallel | lsq_gna_parallel | gradient_descent_parallel
     p_local / args: this rank's shard (use shard()/shard_bounds() to cut them)
+    mode: how the SHARDS agree on stopping (module docstring); the solvers' own mode='retire' goes through **kw as
+          solver_mode='retire' and needs mode='local' here (a retired problem has nothing batch-global left to exchange)
     returns (coeffs_list_local, p_full or None)"""
     from .functions.parallel import _engine
     if mode not in ('local', 'exact', 'exact-peer'):
         raise ValueError("mode must be 'local', 'exact' or 'exact-peer'")
+    if 'solver_mode' in kw:
+        kw['mode'] = kw.pop('solver_mode')
     multi = dist.is_initialized() and dist.get_world_size(group) > 1
     if multi and mode != 'local' and (p_local.shape[0] == 0 or (B_total is not None and B_total < dist.get_world_size(group))):
         # a rank without problems returns before the first iteration and would leave the others waiting in the exchange
