@@ -17,6 +17,8 @@ N=1024 residuals, P=4 parameters, fp64, tol 1e-8, max_iter 80 (README.rst:80-84)
   roofline  dominant kernel of the timed steps, CUDA-event timed per launch INSIDE the timed region (sustained clocks);
             achieved = SURVEY §8(d) algorithmic bytes / average launch duration (fused path: s*N_y per model evaluation)
   also_lm   lsq_lma_parallel meth='lev' on the same batch with its own roofline record (the metric names LM and GN)
+  retire_mode  the opt-in mode='retire' on the same batch (a converged problem is frozen and never evaluated again): problems/s,
+            mean iterations per problem, deviation of its finals from the exact mode — reported separately, not the headline
   tensor_path  K1 (nlls_normal_eq, the HBM-bound kernel of the tensor path) at the same shape: s*C*N*(P+2) bytes per launch
   exact_mode   (N >= 2) sharded solves in modes local / exact (NCCL all-reduce) / exact-peer (nlls_iter_end_peer over NVLink
             peer memory): bit identity with the single-GPU run and microseconds per iteration
@@ -302,6 +304,38 @@ def roofline_record(ctx, kernel, avg_ms, n_live, share, B, C, N, P, esz, per_ste
     return rec
 
 
+def leg_retire(ctx, p0, t, y, w, emg, tol, work, exact_finals, fused):
+    """mode='retire' (not the reference's semantics: reported separately): problems/s, iterations per problem, deviation of the
+    finals from the exact mode on the same batch."""
+    from torchimize_b200.functions import lsq_gna_parallel, lsq_lma_parallel
+    out = {'note': "opt-in mode='retire': a problem whose own stop test fired is frozen at that iterate and never evaluated again "
+                   '(device-resident active list, no host round-trip); NOT the reference semantics, hence not the headline'}
+    B = p0.shape[0]
+    for name, solver, kw in (('gna', lsq_gna_parallel, dict(max_iter=work['max_iter'])), ('lma', lsq_lma_parallel, dict(max_iter=40, meth='lev'))):
+        p = torch.empty_like(p0)
+        st = {}
+
+        def step():
+            p.copy_(p0)
+            return solver(p, emg.cost, emg.jac, args=(t, y), wvec=w, ftol=tol, ptol=tol, gtol=tol, fused=fused, mode='retire', stats=st, **kw)
+        for _ in range(2):
+            step()
+        steps = 3
+        ms, coeffs = ctx.timed(step, steps)
+        stop = st['stop_iteration']
+        iters_pp = torch.where(stop >= 0, stop + 1, torch.full_like(stop, len(coeffs))).double()
+        rec = {'value': B * ctx.world * steps / (ms * 1e-3), 'unit': UNIT, 'ms_per_step': ms / steps, 'iterations': len(coeffs),
+               'mean_iterations_per_problem': float(iters_pp.mean()), 'problems_never_stopped': int((stop < 0).sum())}
+        ex = exact_finals.get(name)
+        if ex is not None:
+            rel = ((p - ex).norm(dim=1) / ex.norm(dim=1))
+            rec['finals_vs_exact_mode'] = {'max_rel': float(rel.max()), 'median_rel': float(rel.median()),
+                                           'note': 'exact mode keeps stepping every problem until all converge together'}
+        out[name] = rec
+        del coeffs
+    return out
+
+
 def leg_tensor_path(ctx, B, C, N, P, dt, esz):
     """K1 alone at the headline shape: the HBM-bound kernel of north_star item (1), driver-visible."""
     from torchimize_b200 import _lib
@@ -548,6 +582,7 @@ def run_ours(args):
     launches = _lib.launches - launches0
     iters = iters_seen[-1]
     del coeffs
+    exact_finals = {'gna': p.clone()}
 
     # ---- the same batch through lsq_lma_parallel meth='lev' (BASELINE.json's metric is quoted for LM and GN): reported
     # beside the headline GN line, same timing rules (resident inputs, CUDA events, per-launch kernel times)
@@ -567,6 +602,7 @@ def run_ours(args):
     ms_lm, _ = ctx.timed(step_lm, lm_steps)
     lm_per = kernel_table(_lib.timing_records())
     _lib.enable_timing(False)
+    exact_finals['lma'] = p.clone()
     lm_top = max(lm_per, key=lambda k: sum(lm_per[k]))
     lm_avg, lm_live = live_average(lm_per[lm_top])
     lm_tot = sum(sum(v) for v in lm_per.values())
@@ -574,6 +610,9 @@ def run_ours(args):
                'iterations': lm_iters[-1], 'value': B * world * lm_steps / (ms_lm * 1e-3), 'unit': UNIT,
                'roofline': roofline_record(ctx, lm_top, lm_avg, len(lm_live), sum(lm_live) / lm_tot if lm_tot else None, B, C, N, P, esz,
                                            {k: sum(v) / lm_steps for k, v in lm_per.items()})}
+
+    retire_rec = leg_retire(ctx, p0, t, y, w, emg, tol, work, exact_finals, fused) if fused else None
+    del exact_finals
 
     # ---- per-kernel breakdown of the timed resident steps (sustained clocks, same launches as `value`)
     per = kernel_table(recs)
@@ -649,6 +688,8 @@ def run_ours(args):
                                'K solves + K result reads inside the timed region)'},
                 'gpu_launches': launches, 'roofline': roof, 'clocks': sampler.summary(), 'also_lm': also_lm,
                 'tensor_path': tensor_rec}
+        if retire_rec is not None:
+            line['retire_mode'] = retire_rec
         if exact_rec is not None:
             line['exact_mode'] = exact_rec
         if cfg5_rec is not None:
