@@ -17,6 +17,12 @@ MODELS = {
 }
 
 if __name__ == '__main__':
+    import shutil
+    keep = set()
     with ThreadPoolExecutor(len(MODELS)) as ex:
         for so in ex.map(lambda kv: _lib.build_plugin(kv[1], kv[0]), MODELS.items()):
             print('built', os.path.relpath(so, ROOT))
+            keep.add(os.path.basename(os.path.dirname(so)))
+    for d in os.listdir(_lib.JIT_DIR):                               # builds of older kernel sources: dead weight in the snapshot
+        if d not in keep:
+            shutil.rmtree(os.path.join(_lib.JIT_DIR, d), ignore_errors=True)

@@ -343,18 +343,42 @@ def test_skewgauss_cases_match_reference(name, dn, P, path):
     _solve_case(gold, name, dn, fun, jac, args, prefix=pre)
 
 
+@pytest.mark.parametrize('path', ['lambdas', 'bound_fused'])
 @pytest.mark.parametrize('dn', ['f64', 'f32'])
 @pytest.mark.parametrize('name', list(PLAIN))
-def test_plain_variants(name, dn):
+def test_plain_variants(name, dn, path):
+    """gna:94-117, gda:90-113.  'bound_fused': the callables of FusedModel.bind(t, y) run the fused kernels (no J)."""
     gold = load('fixtures')
     dt = DT[dn]
     t, y = cu(gold['t'], dt), cu(gold['y'], dt)
     emg = EMGModel(n_costs=2)
     solver, kw = PLAIN[name]
     p = cu(gold['p0'], dt).clone()
-    res = SOLVERS[solver](p, lambda q: emg.cost(q, t, y), lambda q: emg.jac(q, t, y), torch.ones(2, dtype=dt, device=DEV), **kw)
+    if path == 'bound_fused':
+        bm = emg.bind(t, y)
+        fun, jac = bm.cost, bm.jac
+        n0 = _lib.launches
+    else:
+        fun, jac = (lambda q: emg.cost(q, t, y)), (lambda q: emg.jac(q, t, y))
+    res = SOLVERS[solver](p, fun, jac, torch.ones(2, dtype=dt, device=DEV), **kw)
+    if path == 'bound_fused':                                       # 2 launches per iteration (GD: + none, with_masks = 0): no model_eval
+        assert _lib.launches - n0 in (2 * kw['max_iter'], 3 * kw['max_iter'])
     assert res is p
     assert rel_err(res.cpu(), gold[f'{name}__{dn}__p']) <= (1e-10 if dn == 'f64' else 1e-4)
+
+
+def test_bound_model_callables_take_the_fused_path_in_the_conditional_solvers():
+    """FusedModel.bind(t, y): data bound to the callables, args=() — same kernels, same bits as args=(t, y)."""
+    gold = load('synthetic')
+    dt = torch.float64
+    t, y, w = cu(gold['t'], dt), cu(gold['y'], dt), cu(gold['wvec'], dt)
+    emg = EMGModel()
+    bm = emg.bind(t, y)
+    for solver, kw in ((lsq_gna_parallel, {}), (lsq_lma_parallel, dict(meth='lev')), (gradient_descent_parallel, {})):
+        a = torch.stack(solver(cu(gold['p0'], dt).clone(), emg.cost, emg.jac, args=(t, y), wvec=w, max_iter=30, **kw))
+        n0 = _lib.launches
+        b = torch.stack(solver(cu(gold['p0'], dt).clone(), bm.cost, bm.jac, wvec=w, max_iter=30, **kw))
+        assert torch.equal(a, b) and _lib.launches - n0 < 5 * 30 + 8
 
 
 @pytest.mark.parametrize('dn', ['f64', 'f32'])

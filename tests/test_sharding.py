@@ -207,3 +207,39 @@ def test_exact_peer_mode_matches_single_gpu_bit_for_bit_when_two_gpus_are_presen
                         '127.0.0.1', '--master-port', '29533', os.path.join(root, 'scripts', 'peer_exact_check.py')],
                        capture_output=True, text=True, timeout=600)
     assert r.returncode == 0 and 'PEER EXACT CHECK OK' in r.stdout, r.stdout[-2000:] + r.stderr[-2000:]
+
+
+@pytest.mark.gpu
+def test_solvers_run_on_the_device_of_p_not_on_the_current_device_when_two_gpus_are_present():
+    """The reference accepts tensors on any device.  The library launches on the CURRENT device's stream, so every entry
+    point switches to p's device first (_lib.on_device_of): tensors on cuda:1 while cuda:0 is current give the bits of the
+    same solve on cuda:0 — fused and tensor path, the single-problem solver, newton_step_parallel and the host pipeline."""
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip('needs two GPUs on one box')
+    from helpers import load
+    from torchimize_b200.functions import lsq_lma_parallel, lsq_gna_parallel, gradient_descent_parallel, newton_step_parallel, lsq_gna
+    from torchimize_b200.models import EMGModel
+    from torchimize_b200.pipeline import solve_host_batches
+    gold = load('synthetic')
+    dt = torch.float64
+    emg = EMGModel()
+    torch.cuda.set_device(0)
+    out = {}
+    for dev in ('cuda:0', 'cuda:1'):
+        t, y, p0, w = (torch.as_tensor(gold[k]).to(dt).to(dev) for k in ('t', 'y', 'p0', 'wvec'))
+        res = []
+        for solver, kw in ((lsq_gna_parallel, {}), (lsq_lma_parallel, dict(meth='lev')), (gradient_descent_parallel, {})):
+            for fused in (True, False):
+                res.append(torch.stack(solver(p0.clone(), emg.cost, emg.jac, args=(t, y), wvec=w, max_iter=25, fused=fused, **kw)).cpu())
+        _, f, g, H = newton_step_parallel(p0.clone(), lambda q: emg.cost(q, t, y), lambda q: emg.jac(q, t, y), w)
+        res += [f.cpu(), g.cpu(), H.cpu()]
+        one = lsq_gna(p0[0].clone(), lambda q: emg.cost(q[None], t, y[:1])[0, 0], lambda q: emg.jac(q[None], t, y[:1])[0, 0], max_iter=5)
+        res.append(torch.stack([q.detach() for q in one]).cpu())
+        hb = [(p0.cpu().pin_memory(), (t.cpu().pin_memory(), y.cpu().pin_memory()))]
+        for p_fin, n_it in solve_host_batches(lsq_gna_parallel, hb, emg.cost, emg.jac, wvec=w, device=dev, max_iter=25):
+            res.append(p_fin.clone())
+        assert torch.cuda.current_device() == 0
+        out[dev] = res
+    for a, b in zip(out['cuda:0'], out['cuda:1']):
+        assert torch.equal(a, b)

@@ -136,27 +136,38 @@ def build_plugin(source: str, name: str = 'user', verbose=False):
     if os.path.exists(so):
         return so
     os.makedirs(out_dir, exist_ok=True)
-    hdr = os.path.join(out_dir, 'user_model.cuh')
-    with open(hdr, 'w') as f:
-        f.write(source)
-    tmp = so + f'.tmp{os.getpid()}'
-    cmd = ['nvcc', '-O3', '-std=c++17', '-gencode', 'arch=compute_100a,code=sm_100a', '-lineinfo', '-Xcompiler', '-fPIC',
-           f'-DNLLS_USER_MODEL_HEADER="{hdr}"', '-I', CSRC, '-shared', '-o', tmp,
-           os.path.join(CSRC, 'fused_models.cu'), os.path.join(CSRC, 'api.cu'), '-lcudart']
-    try:
-        r = subprocess.run(cmd, capture_output=True, text=True)
-    except FileNotFoundError as e:
-        raise NllsError('compile_model needs nvcc on PATH (CUDA 12.8+ with sm_100a support): ' + str(e)) from e
-    if r.returncode != 0:
-        import shutil
-        shutil.rmtree(out_dir, ignore_errors=True)
-        raise NllsError(f'compiling user model {name!r} failed:\n' + r.stdout[-3000:] + r.stderr[-6000:])
-    os.replace(tmp, so)
-    # older builds of the same model (other kernel-source hashes) are dead weight in the tree: drop them
-    import shutil
-    for d in os.listdir(JIT_DIR):
-        if d.startswith(safe + '_') and d != os.path.basename(out_dir) and len(d) == len(safe) + 17:
-            shutil.rmtree(os.path.join(JIT_DIR, d), ignore_errors=True)
+    # Several ranks may compile the same new model at once (torchrun): one compiles under an exclusive lock on the build
+    # directory, the others wait and find the library.  Header and output are per-process temp names; only finished files
+    # are renamed into place; a failure removes this process's temp files and nothing else.
+    import fcntl
+    with open(os.path.join(out_dir, '.lock'), 'w') as lock:
+        fcntl.flock(lock, fcntl.LOCK_EX)
+        try:
+            if os.path.exists(so):
+                return so
+            hdr = os.path.join(out_dir, f'user_model.{os.getpid()}.cuh')
+            tmp = so + f'.tmp{os.getpid()}'
+            with open(hdr, 'w') as f:
+                f.write(source)
+            cmd = ['nvcc', '-O3', '-std=c++17', '-gencode', 'arch=compute_100a,code=sm_100a', '-lineinfo', '-Xcompiler', '-fPIC',
+                   f'-DNLLS_USER_MODEL_HEADER="{hdr}"', '-I', CSRC, '-shared', '-o', tmp,
+                   os.path.join(CSRC, 'fused_models.cu'), os.path.join(CSRC, 'api.cu'), '-lcudart']
+            try:
+                r = subprocess.run(cmd, capture_output=True, text=True)
+            except FileNotFoundError as e:
+                raise NllsError('compile_model needs nvcc on PATH (CUDA 12.8+ with sm_100a support): ' + str(e)) from e
+            finally:
+                if os.path.exists(hdr) and not os.path.exists(tmp):
+                    os.unlink(hdr)
+            if r.returncode != 0:
+                for leftover in (hdr, tmp):
+                    if os.path.exists(leftover):
+                        os.unlink(leftover)
+                raise NllsError(f'compiling user model {name!r} failed:\n' + r.stdout[-3000:] + r.stderr[-6000:])
+            os.replace(hdr, os.path.join(out_dir, 'user_model.cuh'))     # kept beside the library for reference
+            os.replace(tmp, so)
+        finally:
+            fcntl.flock(lock, fcntl.LOCK_UN)
     if verbose:
         print('built', so)
     return so
@@ -240,6 +251,20 @@ def call(name, *args, lib=None, track=None):
     lib = lib or load()
     if name in TRACKED:
         args = args[:-1] + (ctypes.byref(track) if track is not None else None, args[-1])
+    if _NVTX:                                          # NLLS_NVTX=1: one NVTX range per entry point (K1..K4 in nsys / ncu timelines)
+        torch.cuda.nvtx.range_push(name)
+        try:
+            return _call(lib, name, args)
+        finally:
+            torch.cuda.nvtx.range_pop()
+    return _call(lib, name, args)
+
+
+_NVTX = os.environ.get('NLLS_NVTX') == '1'
+
+
+def _call(lib, name, args):
+    global launches
     if _timing is not None:
         a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         a.record()

@@ -406,7 +406,7 @@ k_model_normal_eq_staged(const T* __restrict__ p, const T* __restrict__ x, const
     if ((lane & (OWN - 1)) == 0) myred[warp * VP + lane / OWN] = v[0];
     __syncthreads();                                         // last tile's stage is free; red and sfc are complete
     if (tid == 0) issue();
-    if (tid < V) {
+    auto write_sums = [&]() {                                // threads 0 .. V-1: g, H, stats[1..2]
       double s = 0.0;
 #pragma unroll
       for (int kk = 0; kk < NW; ++kk) s += myred[kk * VP + tid];
@@ -421,7 +421,8 @@ k_model_normal_eq_staged(const T* __restrict__ p, const T* __restrict__ x, const
       } else {
         stats[b * 4 + (tid - P - NH) + 1] = s;
       }
-    } else if (warp == NW - 1) {                             // sum_c (sum_n f)^2 from the per-thread sums
+    };
+    auto write_cost = [&]() {                                // one whole warp: sum_c (sum_n f)^2 from the per-thread sums
       const double* col = sfc + (size_t)pbuf * C * TPB;
       double tot = 0.0;
       for (int c = 0; c < C; ++c) {
@@ -435,6 +436,13 @@ k_model_normal_eq_staged(const T* __restrict__ p, const T* __restrict__ x, const
         stats[b * 4 + 0] = tot;
         stats[b * 4 + 3] = 0.0;
       }
+    };
+    if constexpr (NW == 1) {                                 // single-warp CTA: the same warp does both, one after the other
+      write_cost();
+      if (tid < V) write_sums();
+    } else {
+      if (tid < V) write_sums();
+      else if (warp == NW - 1) write_cost();
     }
   }
 }
@@ -474,16 +482,18 @@ template <> struct Lane16<double> {
   }
 };
 
-template <typename T, typename Model, int TPB, int NSTAGE>
+// CT > 0: compile-time number of costs (as in k_model_normal_eq_staged): unrolled cost loop, per-cost sums in registers.
+template <typename T, typename Model, int TPB, int NSTAGE, int CT = 0>
 __global__ void __launch_bounds__(TPB, 512 / TPB)
 k_model_normal_eq_vec(const T* __restrict__ p, const T* __restrict__ x, const T* __restrict__ y, long long ybs,
-                      long long ycs, const T* __restrict__ w, int wlen, long long B, int C, int N, T* mA, T* mB,
+                      long long ycs, const T* __restrict__ w, int wlen, long long B, int C_, int N, T* mA, T* mB,
                       T* __restrict__ g, T* __restrict__ H, double* __restrict__ stats, const nlls_ctrl* ctrl,
                       const unsigned char* __restrict__ sel, nlls_track tr) {
   if (is_done(ctrl)) return;
   constexpr int P = Model::P, NW = TPB / 32, NH = Tri<P>::N, V = P + NH + 2, VEC = Lane16<T>::VEC, TN = TPB * VEC;
   constexpr int VP = Pow2Ceil<V>::value, OWN = 32 / VP;
   static_assert(V <= 32, "model with too many parameters for the transposed reduction");
+  const int C = CT > 0 ? CT : C_;
   const int it = iter_index(ctrl);
   const WorkList WL(tr, it, B);
   T* m_out = (it & 1) ? mB : mA;
@@ -546,7 +556,13 @@ k_model_normal_eq_vec(const T* __restrict__ p, const T* __restrict__ x, const T*
     acc.clear();
     double sd = 0.0, sq = 0.0;
     double* my_sfc = sfc + (size_t)pbuf * C * TPB + tid;
-    for (int c = 0; c < C; ++c) my_sfc[c * TPB] = 0.0;
+    [[maybe_unused]] double sfr[CT > 0 ? CT : 1];
+    if constexpr (CT > 0) {
+#pragma unroll
+      for (int c = 0; c < CT; ++c) sfr[c] = 0.0;
+    } else {
+      for (int c = 0; c < C; ++c) my_sfc[c * TPB] = 0.0;
+    }
     if (sel) m_out = sel[b] ? mA : mB;
     T* mo_b = m_out ? m_out + b * (long long)N : nullptr;
     for (int n0 = 0; n0 < N; n0 += TN) {
@@ -564,20 +580,17 @@ k_model_normal_eq_vec(const T* __restrict__ p, const T* __restrict__ x, const T*
       if (live) {
         const T* yc = ring + (size_t)st * stage_elems + tid * VEC;
         T sdt = T(0), sqt = T(0);
-        T yv[VEC], mp[VEC];
-        if (has_prev) Lane16<T>::lds(yc + Cy * TN, mp);
-        Lane16<T>::lds(yc, yv);
-#pragma unroll 2
-        for (int c = 0; c < C; ++c) {
-          const T wc = w[wlen == 1 ? 0 : c];
-          if (c > 0 && ystep) { yc += ystep; Lane16<T>::lds(yc, yv); }
-          T r[VEC], fv[VEC];
+        T mp[VEC];
+        Lane16<T>::lds(yc + Cy * TN, mp);                     // without a previous iterate: stale bytes, replaced by m below
+#pragma unroll
+        for (int j = 0; j < VEC; ++j) mp[j] = has_prev ? mp[j] : m[j];   // f_prev - f == 0 exactly
+        auto cost = [&](const T* yrow, T wc) -> T {            // one cost of this tile; returns the thread's sum of f
+          T yv[VEC], r[VEC], fv[VEC];
+          Lane16<T>::lds(yrow, yv);
 #pragma unroll
           for (int j = 0; j < VEC; ++j) { r[j] = yv[j] - m[j]; fv[j] = mul_rn(r[j], r[j]); }
-          if (has_prev) {                                    // f_prev rebuilt from the stored model value (bit-identical)
 #pragma unroll
-            for (int j = 0; j < VEC; ++j) { const T rp = yv[j] - mp[j]; const T d = mul_rn(rp, rp) - fv[j]; sdt = fma(d, d, sdt); }
-          }
+          for (int j = 0; j < VEC; ++j) { const T rp = yv[j] - mp[j]; const T d = mul_rn(rp, rp) - fv[j]; sdt = fma(d, d, sdt); }
           T sfl = T(0);
 #pragma unroll
           for (int j = 0; j < VEC; ++j) {
@@ -587,7 +600,14 @@ k_model_normal_eq_vec(const T* __restrict__ p, const T* __restrict__ x, const T*
             s2[j] += wf;
             s3[j] = fma(wf, r[j], s3[j]);
           }
-          my_sfc[c * TPB] += (double)sfl;
+          return sfl;
+        };
+        if constexpr (CT > 0) {
+#pragma unroll
+          for (int c = 0; c < CT; ++c) sfr[c] += (double)cost(yc + c * ystep, w[wlen == 1 ? 0 : c]);
+        } else {
+#pragma unroll 2
+          for (int c = 0; c < C; ++c) my_sfc[c * TPB] += (double)cost(yc + c * ystep, w[wlen == 1 ? 0 : c]);
         }
         sd += (double)sdt;
         sq += (double)sqt;
@@ -599,6 +619,10 @@ k_model_normal_eq_vec(const T* __restrict__ p, const T* __restrict__ x, const T*
         if (tid == 0) issue();
       }
       if (++st == NSTAGE) { st = 0; ph ^= 1u; }
+    }
+    if constexpr (CT > 0) {
+#pragma unroll
+      for (int c = 0; c < CT; ++c) my_sfc[c * TPB] = sfr[c];
     }
     double v[VP];
 #pragma unroll
@@ -660,8 +684,8 @@ k_model_normal_eq_vec(const T* __restrict__ p, const T* __restrict__ x, const T*
 // f_prev is rebuilt from it, see the head of this file) or of the cost-summed f_s (GDA); outg/outH are T (NEQ) or fp64 (GDA).
 enum { WPP_NEQ = 0, WPP_GDA = 1, WPP_COST = 2 };
 
-template <typename T, typename Model, int MODE, int SB, int NSTAGE, int NW, bool C1, bool VL = false>
-__global__ void __launch_bounds__(NW * 32)
+template <typename T, typename Model, int MODE, int SB, int NSTAGE, int NW, bool C1, bool VL = false, int MINB = 1>
+__global__ void __launch_bounds__(NW * 32, MINB)
 k_model_wpp(const T* __restrict__ p, const T* __restrict__ x, const T* __restrict__ y, long long ybs, long long ycs,
             const T* __restrict__ w, int wlen, long long B, int C_, int N, T* prevA, T* prevB, void* __restrict__ outg,
             void* __restrict__ outH, double* __restrict__ stats, const nlls_ctrl* ctrl, int CH,
@@ -1200,16 +1224,18 @@ k_model_cost_stat_vec(const T* __restrict__ p, const T* __restrict__ x, const T*
 }
 
 // ------------------------------------------------------------------ fused GD flavour, bulk-copy staged
-template <typename T, typename Model, int TPB, int S, int NSTAGE>
-__global__ void __launch_bounds__(TPB)
+// CT > 0: compile-time number of costs (unrolled cost loop); MINB: CTAs per SM the register allocation aims at.
+template <typename T, typename Model, int TPB, int S, int NSTAGE, int CT = 0, int MINB = 0>
+__global__ void __launch_bounds__(TPB, MINB > 0 ? MINB : 1)
 k_model_normal_eq_gda_staged(const T* __restrict__ p, const T* __restrict__ x, const T* __restrict__ y, long long ybs,
-                             long long ycs, const T* __restrict__ w, int wlen, long long B, int C, int N, T* fsA, T* fsB,
+                             long long ycs, const T* __restrict__ w, int wlen, long long B, int C_, int N, T* fsA, T* fsB,
                              double* __restrict__ g64, double* __restrict__ H64, double* __restrict__ stats,
                              const nlls_ctrl* ctrl, nlls_track tr) {
   if (is_done(ctrl)) return;
   constexpr int P = Model::P, NW = TPB / 32, NH = Tri<P>::N, V = P + NH + 2, TN = TPB * S;
   constexpr int VP = Pow2Ceil<V>::value, OWN = 32 / VP;
   static_assert(V <= 32, "model with too many parameters for the transposed reduction");
+  const int C = CT > 0 ? CT : C_;
   const int it = iter_index(ctrl);
   const WorkList WL(tr, it, B);
   T* __restrict__ fs_out = (it & 1) ? fsB : fsA;
@@ -1243,15 +1269,19 @@ k_model_normal_eq_gda_staged(const T* __restrict__ p, const T* __restrict__ x, c
       T s1[S], fs[S];
 #pragma unroll
       for (int i = 0; i < S; ++i) { s1[i] = T(0); fs[i] = T(0); }
-      const T* yc = sy;
-      for (int c = 0; c < C; ++c, yc += ystep) {
-        const T wc = w[wlen == 1 ? 0 : c];
+      auto cost = [&](const T* yc, T wc) {
 #pragma unroll
         for (int i = 0; i < S; ++i) {
           const T r = yc[i * TPB] - m[i];                    // rows past N hold stale data; masked below
           s1[i] = fma(wc, r, s1[i]);
           fs[i] = fma(wc, r * r, fs[i]);                     // gda:136
         }
+      };
+      if constexpr (CT > 0) {
+#pragma unroll
+        for (int c = 0; c < CT; ++c) cost(sy + c * ystep, w[wlen == 1 ? 0 : c]);
+      } else {
+        for (int c = 0; c < C; ++c) cost(sy + c * ystep, w[wlen == 1 ? 0 : c]);
       }
 #pragma unroll
       for (int i = 0; i < S; ++i) {
@@ -1610,21 +1640,22 @@ static int launch_staged(const ModelArgs& a) {
 }
 
 
-// fp64 default: up to 8 costs as a compile-time constant, 64-thread CTAs with 4 samples per thread, 6 CTAs per SM (166
-// registers, no spills): 20 independent residual chains per thread and tile.  cfg-2 GN fp64 on one box (profiles/r02e):
-// run-time C at 128 x 2: 1.065 ms; compile-time C at 128 x 2 (128 registers): 0.998 ms; at 64 x 4: 0.929 ms.
+// fp64 default: up to 8 costs as a compile-time constant, SINGLE-WARP CTAs with 4 samples per thread, 12 CTAs per SM (168
+// registers): 20 independent residual chains per thread and tile, and no CTA barrier to wait in (10 % of the stalls of the
+// 64-thread shape, profiles/r02n).  cfg-2 GN fp64 (profiles/r02e, r02k): run-time C at 128 x 2: 1.065 ms; compile-time C at
+// 128 x 2 (128 registers): 0.998 ms; at 64 x 4: 0.929 ms (0.923 on the r02k box); at 32 x 4: 0.894 ms on that box.
 template <typename T, typename Model>
 static int launch_staged_ct(const ModelArgs& a) {
   if constexpr (sizeof(T) == 8) {
     switch (a.C) {
-      case 1: return launch_staged<T, Model, 64, 4, 1, 6>(a);
-      case 2: return launch_staged<T, Model, 64, 4, 2, 6>(a);
-      case 3: return launch_staged<T, Model, 64, 4, 3, 6>(a);
-      case 4: return launch_staged<T, Model, 64, 4, 4, 6>(a);
-      case 5: return launch_staged<T, Model, 64, 4, 5, 6>(a);
-      case 6: return launch_staged<T, Model, 64, 4, 6, 6>(a);
-      case 7: return launch_staged<T, Model, 64, 4, 7, 6>(a);
-      case 8: return launch_staged<T, Model, 64, 4, 8, 6>(a);
+      case 1: return launch_staged<T, Model, 32, 4, 1, 12>(a);
+      case 2: return launch_staged<T, Model, 32, 4, 2, 12>(a);
+      case 3: return launch_staged<T, Model, 32, 4, 3, 12>(a);
+      case 4: return launch_staged<T, Model, 32, 4, 4, 12>(a);
+      case 5: return launch_staged<T, Model, 32, 4, 5, 12>(a);
+      case 6: return launch_staged<T, Model, 32, 4, 6, 12>(a);
+      case 7: return launch_staged<T, Model, 32, 4, 7, 12>(a);
+      case 8: return launch_staged<T, Model, 32, 4, 8, 12>(a);
       default: break;
     }
   }
@@ -1632,8 +1663,9 @@ static int launch_staged_ct(const ModelArgs& a) {
 }
 
 // 128-bit-lane staged kernel: same eligibility as launch_staged plus a 16-byte aligned abscissa
-template <typename T, typename Model, int TPB2>
+template <typename T, typename Model, int TPB2, int CT = 0>
 static int launch_vec(const ModelArgs& a) {
+  if (CT > 0 && a.C != CT) return 1;
   constexpr int P = Model::P, V = P + Tri<P>::N + 2, NW2 = TPB2 / 32, TN = TPB2 * Lane16<T>::VEC, VP = Pow2Ceil<V>::value;
   const size_t es = sizeof(T);
   const int Cy = a.ycs == 0 ? 1 : a.C;
@@ -1651,8 +1683,8 @@ static int launch_vec(const ModelArgs& a) {
     kern2<<<grid2, TPB2, smem2, a.st>>>((const T*)a.p, (const T*)a.x, (const T*)a.y, a.ybs, a.ycs, (const T*)a.w, a.wlen,
                                         a.B, a.C, a.N, (T*)a.fA, (T*)a.fB, (T*)a.g, (T*)a.H, a.stats, a.ctrl, a.sel, a.tr);
   };
-  if (three) launch(k_model_normal_eq_vec<T, Model, TPB2, 3>);
-  else launch(k_model_normal_eq_vec<T, Model, TPB2, 2>);
+  if (three) launch(k_model_normal_eq_vec<T, Model, TPB2, 3, CT>);
+  else launch(k_model_normal_eq_vec<T, Model, TPB2, 2, CT>);
   return check_launch("nlls_model_normal_eq(vec)");
 }
 
@@ -1676,8 +1708,11 @@ static int launch_wpp(const ModelArgs& a) {
   const bool c1 = a.C == 1;
   // single-cost problems with a 16-byte aligned abscissa: vector lanes (blocks of 32 * 16/sizeof(T) samples)
   const bool vl = c1 && aligned_to(a.x, 16) && wpp_vector_lanes();
+  static int chmax = -1, minb = -1;                           // tuning hooks: NLLS_WPP_CHMAX (samples per chunk), NLLS_WPP_MINB (CTAs per SM)
+  if (chmax < 0) { const char* e = getenv("NLLS_WPP_CHMAX"); chmax = e ? atoi(e) : 512; }
+  if (minb < 0) { const char* e = getenv("NLLS_WPP_MINB"); minb = e ? atoi(e) : 0; }
   int CH = vl ? 128 : 64;
-  while (CH < 512 && CH < a.N && (size_t)(Cy + CP) * (CH * 2) * es <= 4096) CH *= 2;
+  while (CH < chmax && CH < a.N && (size_t)(Cy + CP) * (CH * 2) * es <= 4096) CH *= 2;
   const bool use_sfc = !c1 && MODE != WPP_GDA;
   const size_t per_warp = (size_t)NSTAGE * (Cy + CP) * CH * es + 64 + (use_sfc ? (size_t)a.C * 32 * 8 : 0);
   const size_t smem = per_warp * NW;
@@ -1691,10 +1726,35 @@ static int launch_wpp(const ModelArgs& a) {
                                         a.C, a.N, (T*)a.fA, (T*)a.fB, og, oH, os, a.ctrl, CH, MODE == WPP_NEQ ? a.sel : nullptr,
                                         MODE == WPP_COST ? nlls_track{} : a.tr);
   };
+#ifndef NLLS_USER_MODEL_HEADER
+  if (vl && minb == 5) go(k_model_wpp<T, Model, MODE, 16 / (int)sizeof(T), NSTAGE, NW, true, true, 5>);
+  else if (vl && minb == 6) go(k_model_wpp<T, Model, MODE, 16 / (int)sizeof(T), NSTAGE, NW, true, true, 6>);
+  else if (vl && minb == 8) go(k_model_wpp<T, Model, MODE, 16 / (int)sizeof(T), NSTAGE, NW, true, true, 8>);
+  else
+#endif
   if (vl) go(k_model_wpp<T, Model, MODE, 16 / (int)sizeof(T), NSTAGE, NW, true, true>);
   else if (c1) go(k_model_wpp<T, Model, MODE, SB, NSTAGE, NW, true>);
   else go(k_model_wpp<T, Model, MODE, SB, NSTAGE, NW, false>);
   return check_launch("nlls_model(wpp)");
+}
+
+// fp32 default: 128-bit lanes, 64-thread CTAs, up to 8 costs as a compile-time constant
+template <typename T, typename Model>
+static int launch_vec_ct(const ModelArgs& a) {
+  if constexpr (sizeof(T) == 4) {
+    switch (a.C) {
+      case 1: return launch_vec<T, Model, 64, 1>(a);
+      case 2: return launch_vec<T, Model, 64, 2>(a);
+      case 3: return launch_vec<T, Model, 64, 3>(a);
+      case 4: return launch_vec<T, Model, 64, 4>(a);
+      case 5: return launch_vec<T, Model, 64, 5>(a);
+      case 6: return launch_vec<T, Model, 64, 6>(a);
+      case 7: return launch_vec<T, Model, 64, 7>(a);
+      case 8: return launch_vec<T, Model, 64, 8>(a);
+      default: break;
+    }
+  }
+  return launch_vec<T, Model, 64>(a);
 }
 
 template <typename T>
@@ -1743,13 +1803,14 @@ static int launch_cost_vec(const ModelArgs& a) {
   return check_launch("nlls_model_cost_stat(vec)");
 }
 
-template <typename T, typename Model, int TPB2, int S2>
+template <typename T, typename Model, int TPB2, int S2, int CT = 0, int MINB = 0>
 static int launch_gda_staged(const ModelArgs& a) {
   constexpr int P = Model::P, V = P + Tri<P>::N + 2, NW2 = TPB2 / 32, TN = TPB2 * S2, VP = Pow2Ceil<V>::value;
+  if (CT > 0 && a.C != CT) return 1;
   if (!rows16<T>(a) || (a.fA && !(aligned_to(a.fA, 16) && aligned_to(a.fB, 16)))) return 1;
   const int Cy = a.ycs == 0 ? 1 : a.C;
   const size_t tail = (size_t)2 * NW2 * VP * 8;
-  const int want_ctas = 512 / TPB2;
+  const int want_ctas = MINB > 0 ? MINB : 512 / TPB2;
   const bool three = (size_t)want_ctas * (TileRing<T, TN, 3>::bytes(Cy, 1) + tail + 1024) <= 226 * 1024;
   const size_t smem2 = (three ? TileRing<T, TN, 3>::bytes(Cy, 1) : TileRing<T, TN, 2>::bytes(Cy, 1)) + tail;
   if (smem2 > 220 * 1024) return 1;
@@ -1758,8 +1819,8 @@ static int launch_gda_staged(const ModelArgs& a) {
     kern2<<<grid2, TPB2, smem2, a.st>>>((const T*)a.p, (const T*)a.x, (const T*)a.y, a.ybs, a.ycs, (const T*)a.w, a.wlen, a.B,
                                         a.C, a.N, (T*)a.fA, (T*)a.fB, a.g64, a.H64, a.stats, a.ctrl, a.tr);
   };
-  if (three) launch(k_model_normal_eq_gda_staged<T, Model, TPB2, S2, 3>);
-  else launch(k_model_normal_eq_gda_staged<T, Model, TPB2, S2, 2>);
+  if (three) launch(k_model_normal_eq_gda_staged<T, Model, TPB2, S2, 3, CT, MINB>);
+  else launch(k_model_normal_eq_gda_staged<T, Model, TPB2, S2, 2, CT, MINB>);
   return check_launch("nlls_model_normal_eq_gda(staged)");
 }
 
@@ -1801,12 +1862,14 @@ static int run_op(Op op, const ModelArgs& a) {
           case 7: rc = launch_vec<T, Model, 256>(a); break;
           case 8: rc = launch_staged<T, Model, 128, 2, 5, 4>(a); break;       // compile-time C = 5 at other CTA shapes
           case 10: rc = launch_staged<T, Model, 128, 2, 5, 3>(a); break;
+          case 12: rc = launch_staged<T, Model, 64, 4, 5, 6>(a); break;       // the round-2 64 x 4 shape
+          case 13: rc = launch_staged<T, Model, 32, 8, 5, 8>(a); break;
           case 11: rc = launch_staged<T, Model, 128, 2, 0, 0>(a); break;      // run-time C (the C > 8 kernel)
 #endif
           default:
             // fp32: 128-bit lanes, 64-thread CTAs (cfg-2 fp32 1.01 -> 0.76 ms, profiles/r01f); fp64 is HBM-bound either
             // way and measures a little better with the strided map at 4 CTAs/SM (r01 sweeps)
-            if (vec_family<T>()) rc = launch_vec<T, Model, 64>(a);
+            if (vec_family<T>()) rc = launch_vec_ct<T, Model>(a);
             if (rc == 1) rc = launch_staged_ct<T, Model>(a);
             break;
         }
@@ -1824,7 +1887,21 @@ static int run_op(Op op, const ModelArgs& a) {
           const int rcw = launch_wpp<T, Model, WPP_GDA>(a);
           if (rcw <= 0) return rcw;
         }
-        const int rc = launch_gda_staged<T, Model, 128, 2>(a);
+        int rc = 1;
+        if constexpr (sizeof(T) == 8) {                        // fp64: the NEQ kernel's shape (single-warp CTAs, 4 samples per thread, compile-time C)
+          switch (fused_variant() == 0 ? a.C : 0) {
+            case 1: rc = launch_gda_staged<T, Model, 32, 4, 1, 12>(a); break;
+            case 2: rc = launch_gda_staged<T, Model, 32, 4, 2, 12>(a); break;
+            case 3: rc = launch_gda_staged<T, Model, 32, 4, 3, 12>(a); break;
+            case 4: rc = launch_gda_staged<T, Model, 32, 4, 4, 12>(a); break;
+            case 5: rc = launch_gda_staged<T, Model, 32, 4, 5, 12>(a); break;
+            case 6: rc = launch_gda_staged<T, Model, 32, 4, 6, 12>(a); break;
+            case 7: rc = launch_gda_staged<T, Model, 32, 4, 7, 12>(a); break;
+            case 8: rc = launch_gda_staged<T, Model, 32, 4, 8, 12>(a); break;
+            default: break;
+          }
+        }
+        if (rc == 1) rc = launch_gda_staged<T, Model, 128, 2>(a);
         if (rc <= 0) return rc;
       }
       auto kern = k_model_normal_eq_gda<T, Model, TPB>;
@@ -1851,7 +1928,7 @@ static int run_op(Op op, const ModelArgs& a) {
         if (vec_family<T>()) rc = launch_cost_vec<T, Model, 64>(a);
         // same sample-to-thread map as the normal-equation kernel of the same shape (launch_staged_ct): the two-pass and
         // the speculative LM schedules see the same bits in stats[0]
-        if (rc == 1 && sizeof(T) == 8 && a.C <= 8) rc = launch_cost_staged<T, Model, 64, 4>(a);
+        if (rc == 1 && sizeof(T) == 8 && a.C <= 8) rc = launch_cost_staged<T, Model, 32, 4>(a);
         if (rc == 1) rc = launch_cost_staged<T, Model, 128, 2>(a);
         if (rc <= 0) return rc;
       }

@@ -18,7 +18,7 @@ import warnings
 import torch
 
 from ... import _lib
-from ...models import fused_model_of, model_owner_of
+from ...models import bound_model_of, fused_model_of, model_owner_of
 from ..jacobian import batch_jacobian_approx_t
 
 GN, LM, GD = _lib.SOLVER_GN, _lib.SOLVER_LM, _lib.SOLVER_GD
@@ -205,6 +205,10 @@ def solve(solver, p, function, jac_function, args, wvec, ftol, ptol, gtol, max_i
     # 'lm' = speculative schedule (nlls_model_lm_trial), 'lm2' = two-pass schedule (needs nlls_model_cost_stat)
     skey = {GN: 'gn', LM: 'lm' if SPECULATIVE_LM else 'lm2', GD: 'gd'}[solver]
     model = fused_model_of(function, jac_function, skey) if fused else None
+    if model is None and fused and len(args) == 0:          # FusedModel.bind(x, y): the data travels with the callables
+        bound = bound_model_of(function, jac_function, skey)
+        if bound is not None:
+            model, args = bound
     st = _lib.stream_ptr
     B, P, code = ws.B, ws.P, ws.code
     ctrl = _lib.ptr(ws.ctrl)
@@ -352,7 +356,10 @@ def solve(solver, p, function, jac_function, args, wvec, ftol, ptol, gtol, max_i
                 f_h = _as_work(fun(ws.p_trial), ws.dtype, 'function', (B, C, N))       # lma:99
                 _lib.call('nlls_cost_stat', code, _lib.ptr(f_h), B, C, N, _lib.ptr(ws.stat_h), ctrl, st())
             update(hp)
-            f_prev = keep                                   # pointer swap instead of f.clone() (lma:111)
+            # the reference clones (lma:111, gna:81).  Our own model kernels hand out a fresh tensor per call, so the pointer
+            # is enough there; an opaque user callable may write into a buffer it reuses (out=...), which would make f_prev
+            # alias the next f and fire fcon at once: clone
+            f_prev = keep if (owner is not None or solver == GD) else keep.clone()
             done, iters, sing = ws.flags()
             if done:
                 break
@@ -371,26 +378,36 @@ def solve(solver, p, function, jac_function, args, wvec, ftol, ptol, gtol, max_i
 
 @_lib.on_device_of(1)
 def plain(solver, p, function, jac_function, wvec, l, max_iter):
-    """Fixed-iteration variants (gna:94-117, gda:90-113): no stop tests, returns the final p."""
+    """Fixed-iteration variants (gna:94-117, gda:90-113): no stop tests, returns the final p.  Callables of a
+    FusedModel.bind(x, y) run the fused kernels (no Jacobian tensor, nothing kept between iterations)."""
     _check_p(p)
     work_p = p if p.is_contiguous() else p.contiguous()
     ws = Workspace(work_p, wvec, solver)
     B, P, code = ws.B, ws.P, ws.code
     st = _lib.stream_ptr
+    bound = bound_model_of(function, jac_function, 'gd' if solver == GD else 'gn')
+    if bound is not None:
+        model, margs = bound
+        x, y, ybs, ycs, C, N = model.layout(work_p, *margs)
+        if ws.w.numel() not in (1, C):
+            raise _lib.NllsError(f'wvec has {ws.w.numel()} entries for {C} costs')
     for _ in range(max_iter):
-        f = _as_work(function(work_p), ws.dtype, 'function')
-        _, C, N = f.shape
-        J = _as_work(jac_function(work_p), ws.dtype, 'jac_function', (B, C, N, P))
-        if solver == GD:
-            _lib.call('nlls_normal_eq_gda', code, _lib.ptr(J), _lib.ptr(f), None, _lib.ptr(ws.w), ws.w.numel(), B, C, N, P,
-                      _lib.ptr(ws.g), _lib.ptr(ws.H), None, _lib.ptr(ws.stats), None, st())
-            _lib.call('nlls_gd_update', code, _lib.ptr(work_p), _lib.ptr(ws.g), _lib.ptr(ws.H), None, float(l), 0., 0., 0., 0,
-                      B, P, None, None, None, st())
+        if bound is not None:
+            name = 'nlls_model_normal_eq_gda' if solver == GD else 'nlls_model_normal_eq'
+            _lib.call(name, model.model_id, code, _lib.ptr(work_p), P, _lib.ptr(x), _lib.ptr(y), ybs, ycs, _lib.ptr(ws.w),
+                      ws.w.numel(), B, C, N, None, None, _lib.ptr(ws.g), _lib.ptr(ws.H), _lib.ptr(ws.stats), None, st(), lib=model.lib)
         else:
-            _lib.call('nlls_normal_eq', code, _lib.ptr(J), _lib.ptr(f), None, _lib.ptr(ws.w), ws.w.numel(), B, C, N, P,
-                      _lib.ptr(ws.g), _lib.ptr(ws.H), _lib.ptr(ws.stats), None, st())
-            _lib.call('nlls_gn_update', code, _lib.ptr(work_p), _lib.ptr(ws.g), _lib.ptr(ws.H), None, float(l), 0., 0., 0., 0,
-                      B, P, None, None, None, st())
+            f = _as_work(function(work_p), ws.dtype, 'function')
+            _, C, N = f.shape
+            J = _as_work(jac_function(work_p), ws.dtype, 'jac_function', (B, C, N, P))
+            if solver == GD:
+                _lib.call('nlls_normal_eq_gda', code, _lib.ptr(J), _lib.ptr(f), None, _lib.ptr(ws.w), ws.w.numel(), B, C, N, P,
+                          _lib.ptr(ws.g), _lib.ptr(ws.H), None, _lib.ptr(ws.stats), None, st())
+            else:
+                _lib.call('nlls_normal_eq', code, _lib.ptr(J), _lib.ptr(f), None, _lib.ptr(ws.w), ws.w.numel(), B, C, N, P,
+                          _lib.ptr(ws.g), _lib.ptr(ws.H), _lib.ptr(ws.stats), None, st())
+        _lib.call('nlls_gd_update' if solver == GD else 'nlls_gn_update', code, _lib.ptr(work_p), _lib.ptr(ws.g), _lib.ptr(ws.H),
+                  None, float(l), 0., 0., 0., 0, B, P, None, None, None, st())
     if work_p is not p:
         p.copy_(work_p)
     return p

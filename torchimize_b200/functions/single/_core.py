@@ -32,7 +32,10 @@ def _work(t, dtype, what, shape=None):
     _lib.require_cuda(t)
     if shape is not None and tuple(t.shape) != tuple(shape):
         raise _lib.NllsError(f'{what} returned shape {tuple(t.shape)}, expected {tuple(shape)}')
-    return t.detach().to(dtype).contiguous()
+    w = t.detach().to(dtype).contiguous()
+    # a private copy (the reference clones f, lma_fun_single.py:89): a callable that reuses its output buffer must not
+    # make the kept residuals alias the next evaluation
+    return w.clone() if w.data_ptr() == t.data_ptr() else w
 
 
 class Single:
@@ -120,20 +123,29 @@ def lsq_lma(p, function, jac_function, args, ftol, ptol, gtol, tau, meth, rho1, 
     u, v = tau * torch.max(torch.diag(Hc)), 2                    # lma_fun_single.py:72-73
     out = [p]
     pd = p.detach()
+    marquardt = meth != 'lev'
     while len(out) < max_iter:
-        D = torch.eye(P)                                         # float32 on purpose (lma:76)
-        D *= 1 if meth == 'lev' else torch.max(torch.maximum(Hc.diagonal(), D.diagonal()))
-        damp = (u * D)[0, 0]                                     # the scalar on the diagonal of u*D (lma:78)
+        # Damping added to the diagonal: u times the scale of the reference's D (lma_fun_single.py:76-78).  D starts as a
+        # float32 identity there, so scale and product are rounded to float32 whatever the problem's dtype — kept, since the
+        # trajectories depend on it.  Levenberg: scale 1.  Marquardt: the largest of max diag(H) and 1.
+        scale = Hc.diagonal().max().clamp_min(1.).to(torch.float32) if marquardt else torch.ones((), dtype=torch.float32)
+        damp = u.to(torch.float32) * scale
         h = S.solve(g[None], H[None], pd[None], damp)
         hc = h.cpu()
         p_try = pd + h
         f_h = _work(fun(p_try), dt, 'function', (N,))
         fh2, _ = S.sumsq(f_h)
-        den = hc @ (u * hc - gc)                                 # lma:80
-        num = torch.tensor(ff - fh2, dtype=dt)                   # lma:81 (sums in fp64 here)
-        rho = num / den if den > 0 else torch.inf if num > 0 else -torch.inf
+        # gain ratio (lma:80-82): cost decrease over the decrease the damped quadratic model predicts; a model that predicts
+        # no decrease gives +-inf by the sign of the actual change
+        predicted = hc @ (u * hc - gc)
+        actual = torch.tensor(ff - fh2, dtype=dt)                # sums in fp64 here
+        if predicted > 0:
+            rho = actual / predicted
+        else:
+            rho = torch.tensor(float('inf') if actual > 0 else -float('inf'))
+        accepted = bool(rho > 0)
         f_new = f
-        if rho > 0:                                              # lma:83-87
+        if accepted:                                             # lma:83-87
             pd = p_try
             f_new = f_h                                          # fun(p) at the accepted point is the trial evaluation
             j = _work(jac(pd), dt, 'jac_function', (N, P))
@@ -142,10 +154,16 @@ def lsq_lma(p, function, jac_function, args, ftol, ptol, gtol, tau, meth, rho1, 
         out.append(pd.clone())
         ff_new, sd = S.sumsq(f_new, f)                           # lma:89-90, 99
         f, ff = f_new, ff_new
-        if meth == 'lev':                                        # lma:91-94
-            u, v = (u * torch.max(torch.tensor([1 / 3, 1 - (2 * rho - 1) ** 3])), 2) if rho > 0 else (u * v, v * 2)
-        else:
-            u = u * bet if rho < rho1 else u / gam if rho > rho2 else u
+        if not marquardt:                                        # Nielsen's rule (lma:91-92), factor in rho's dtype as there
+            if accepted:
+                shrink = (1 - (2 * rho - 1) ** 3).clamp_min(1 / 3)
+                u, v = u * shrink, 2
+            else:
+                u, v = u * v, v * 2
+        elif rho < rho1:                                         # Marquardt's rule (lma:93-94)
+            u = u * bet
+        elif rho > rho2:
+            u = u / gam
         if stop(gc, hc, pd.cpu(), ff, sd, ftol, ptol, gtol, f_gate=bool(rho > 0)):
             break
     return out

@@ -74,6 +74,25 @@ class FusedModel:
     def cost_and_jac(self, p, x, y):
         return self._eval(p, x, y, True)
 
+    def bind(self, x, y):
+        """The model with its data bound: ``.cost(p)`` / ``.jac(p)`` — the one-argument callables that
+        lsq_gna_parallel_plain / gradient_descent_parallel_plain / newton_step_parallel take (gna:94-101, gda:90-97,
+        newton_parallel.py:21-26).  The solvers recognise them and run the fused kernels (no Jacobian tensor)."""
+        return BoundModel(self, x, y)
+
+
+class BoundModel:
+    """FusedModel + data (see FusedModel.bind)."""
+
+    def __init__(self, model, x, y):
+        self.model, self.args = model, (x, y)
+
+    def cost(self, p):
+        return self.model.cost(p, *self.args)
+
+    def jac(self, p):
+        return self.model.jac(p, *self.args)
+
 
 class EMGModel(FusedModel):
     model_id = _lib.MODEL_EMG
@@ -160,3 +179,17 @@ def fused_model_of(function, jac_function, solver=None):
     if getattr(jac_function, '__self__', None) is owner and getattr(jac_function, '__func__', None) is FusedModel.jac:
         return owner
     return None
+
+
+def bound_model_of(function, jac_function, solver=None):
+    """(model, args) when both callables are the ``cost`` / ``jac`` of one BoundModel whose model has fused kernels for
+    `solver`, else None."""
+    owner = getattr(function, '__self__', None)
+    if not isinstance(owner, BoundModel) or getattr(function, '__func__', None) is not BoundModel.cost:
+        return None
+    if solver is not None and solver not in owner.model.fused_solvers:
+        return None
+    if jac_function is not None and not (getattr(jac_function, '__self__', None) is owner and
+                                         getattr(jac_function, '__func__', None) is BoundModel.jac):
+        return None
+    return owner.model, owner.args
