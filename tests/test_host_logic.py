@@ -61,3 +61,47 @@ def test_single_problem_jacobian_and_binding():
     assert calls == [('f', 1, 2), ('j', 1, 2)]
     fun0, _ = bind_callables(lambda q: q + 1, None, ())              # args empty: function is used as is (lma:62-64)
     assert torch.equal(fun0(p), p + 1)
+
+
+def test_track_struct_matches_the_header_and_is_inserted_before_the_stream_argument():
+    """nlls_track (include/nlls_b200.h): 3 pointers + 2 ints + a 64-bit count = 40 bytes; every TRACKED entry point has the
+    struct pointer as its last argument before `stream`."""
+    import ctypes
+    import os
+    import re
+    from conftest import ROOT
+    from torchimize_b200 import _lib
+    assert ctypes.sizeof(_lib.Track) == 40
+    assert [f[0] for f in _lib.Track._fields_] == ['pstat', 'active', 'count', 'retire', 'reserved', 'B']
+    hdr = open(os.path.join(ROOT, 'include', 'nlls_b200.h')).read()
+    decl = {m.group(1): m.group(2) for m in re.finditer(r'\nint (nlls_\w+)\(([^;]*?)\);', hdr, re.S)}
+    with_track = {n for n, a in decl.items() if 'const nlls_track* track' in a}
+    assert with_track == set(_lib.TRACKED)
+    for n in with_track:
+        args = [a.strip() for a in re.sub(r'/\*.*?\*/', '', decl[n], flags=re.S).split(',')]
+        assert args[-1].startswith('void* stream') and 'nlls_track' in args[-2], n
+        assert _lib.SIGNATURES[n][-2] is _lib._tp
+
+
+def test_bound_model_callables_are_recognised_and_validated_without_a_gpu():
+    import pytest
+    from torchimize_b200 import _lib
+    from torchimize_b200.models import EMGModel, bound_model_of, fused_model_of
+    emg = EMGModel()
+    x, y = torch.zeros(8), torch.zeros(3, 8)
+    bm = emg.bind(x, y)
+    assert bound_model_of(bm.cost, bm.jac, 'gn') == (emg, (x, y))
+    assert bound_model_of(bm.cost, None, 'gd') == (emg, (x, y))            # jac_function=None: the model's analytic Jacobian
+    assert bound_model_of(bm.cost, emg.bind(x, y).jac) is None                # callables of two different bindings
+    assert bound_model_of(emg.cost, emg.jac) is None and fused_model_of(bm.cost, bm.jac) is None
+    assert bound_model_of(lambda p: p, None) is None
+    with pytest.raises(_lib.NllsError, match='CUDA'):                         # no CPU path, with or without binding
+        bm.cost(torch.zeros(3, 4))
+
+
+def test_solver_mode_is_validated_before_anything_touches_the_device():
+    import pytest
+    from torchimize_b200 import _lib
+    from torchimize_b200.functions import lsq_gna_parallel
+    with pytest.raises(_lib.NllsError, match='CUDA'):
+        lsq_gna_parallel(torch.zeros(2, 4), lambda p: p, mode='retire')
