@@ -7,7 +7,7 @@ fp32 and fp64, GN and LM through the public drop-in API (fused path).  One proce
 
 Strong scaling: B is the TOTAL number of problems; rank r holds shard_bounds(B, world, r).  No per-iteration
 collective (mode 'local'); one all-gather of the finals inside the timed region.  A shard that does not fit in HBM
-(fp64 needs 3 x 41 KB per problem for y and the two f buffers) is solved in sequential chunks (--chunk).
+(fp64 needs 57 KB per problem for y and the two model-value buffers) is solved in sequential chunks (--chunk).
 One JSON line per (dtype, solver); times are CUDA-event times, max over ranks."""
 import argparse
 import json
@@ -56,7 +56,7 @@ def main():
         dt = torch.float64 if dn == 'f64' else torch.float32
         es = 8 if dn == 'f64' else 4
         free = torch.cuda.mem_get_info(dev)[0]
-        per_problem = 3 * C * N * es + 4096                          # y + two f buffers (+ small per-problem state)
+        per_problem = (C + 2) * N * es + 4096                        # y + the two model-value buffers (+ small per-problem state)
         chunk = args.chunk or min(mine, int(free * .85) // per_problem)
         n_chunks = (mine + chunk - 1) // chunk
         chunk = (mine + n_chunks - 1) // n_chunks
@@ -114,7 +114,7 @@ def main():
             if rank == 0:
                 it = max(iters)
                 passes = it + (1 if sv == 'lm' else 0)               # speculative LM: one model pass per iteration + the first
-                alg = 3 * es * C * N * mine * passes                 # y + f_cur + f_new per pass
+                alg = es * C * N * mine * passes                     # s*N_y per model evaluation
                 print(json.dumps({'case': f'cfg5-{sv}-{dn}', 'B_total': args.B, 'n_gpus': world, 'B_per_gpu': mine,
                                   'chunks_per_gpu': n_chunks, 'iterations': it, 'ms': ms, 'solve_ms_rank0': solve_ms, 'gather_ms_rank0': gather_ms, 'problems_per_s': args.B / (ms * 1e-3),
                                   'problem_iters_per_s': args.B * it / (ms * 1e-3),
