@@ -1,5 +1,6 @@
 // common.cuh — shared device/host helpers for the sm_100a NLLS kernels.
 #pragma once
+#include <cuda.h>            // CUtensorMap and its enums only: the encoder is fetched at run time, nothing links against libcuda
 #include <cuda_runtime.h>
 #include <cstdint>
 #include <cstdio>
@@ -191,6 +192,16 @@ __device__ __forceinline__ void bulk_g2s(void* dst_smem, const void* src_gmem, u
   asm volatile(
       "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(dst_smem)),
       "l"(src_gmem), "r"(bytes), "r"(smem_u32(bar))
+      : "memory");
+}
+
+// 3-D tiled tensor copy global -> shared through a tensor map (SASS: UTMALDG.3D): ONE instruction moves a box of
+// [c2: 1][c1: rows][c0: samples] elements; completion (always the full box's bytes) on an mbarrier.  dst 128-byte aligned.
+__device__ __forceinline__ void tma_load_3d(void* dst_smem, const CUtensorMap* tm, int c0, int c1, int c2, uint64_t* bar) {
+  asm volatile(
+      "cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];" ::"r"(
+          smem_u32(dst_smem)),
+      "l"(tm), "r"(c0), "r"(c1), "r"(c2), "r"(smem_u32(bar))
       : "memory");
 }
 

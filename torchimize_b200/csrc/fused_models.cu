@@ -174,6 +174,7 @@ struct TileRing {
   const T *a, *bsrc;
   long long a_bs, a_rs, b_bs, b_rs;
   int nA, nB, N, stage_elems;
+  const CUtensorMap* tm; // set A through ONE tensor copy per tile (N % TN == 0), or NULL = one bulk copy per row
   const int* wlist;      // work list (retire mode) or NULL = every problem
   long long wn, pw;      // work items, producer: next work index
   long long pb;          // producer: next problem
@@ -181,7 +182,9 @@ struct TileRing {
   int st;                // consumer: current stage
   unsigned ph;           // consumer: current parity
   __device__ __forceinline__ void init(unsigned char* smem, const T* a_, long long a_bs_, long long a_rs_, int nA_,
-                                       const T* b_, long long b_bs_, long long b_rs_, int nB_, const WorkList& WL, int N_) {
+                                       const T* b_, long long b_bs_, long long b_rs_, int nB_, const WorkList& WL, int N_,
+                                       const CUtensorMap* tm_ = nullptr) {
+    tm = tm_;
     a = a_; a_bs = a_bs_; a_rs = a_rs_; nA = nA_;
     bsrc = b_; b_bs = b_bs_; b_rs = b_rs_; nB = b_ ? nB_ : 0;
     wlist = WL.list; wn = WL.n; N = N_;
@@ -211,8 +214,13 @@ struct TileRing {
     T* dst = ring + (size_t)pst * stage_elems;
     uint64_t* bar = &bars[pst];
     mbar_expect_tx(bar, nbytes * (unsigned)(nA + nB));
-    const T* src = a + pb * a_bs + pn0;
-    for (int r = 0; r < nA; ++r, src += a_rs, dst += TN) bulk_g2s(dst, src, nbytes, bar);
+    if (tm) {
+      tma_load_3d(dst, tm, pn0, 0, (int)pb, bar);
+      dst += nA * TN;
+    } else {
+      const T* src = a + pb * a_bs + pn0;
+      for (int r = 0; r < nA; ++r, src += a_rs, dst += TN) bulk_g2s(dst, src, nbytes, bar);
+    }
     if (nB) {
       const T* s2 = bsrc + pb * b_bs + pn0;
       for (int r = 0; r < nB; ++r, s2 += b_rs, dst += TN) bulk_g2s(dst, s2, nbytes, bar);
@@ -246,7 +254,8 @@ __global__ void __launch_bounds__(TPB, MINB > 0 ? MINB : 512 / TPB)
 k_model_normal_eq_staged(const T* __restrict__ p, const T* __restrict__ x, const T* __restrict__ y, long long ybs,
                          long long ycs, const T* __restrict__ w, int wlen, long long B, int C_, int N, T* mA, T* mB,
                          T* __restrict__ g, T* __restrict__ H, double* __restrict__ stats, const nlls_ctrl* ctrl,
-                         const unsigned char* __restrict__ sel, nlls_track tr) {
+                         const unsigned char* __restrict__ sel, nlls_track tr, const __grid_constant__ CUtensorMap tmy,
+                         int use_tm) {
   if (is_done(ctrl)) return;
   constexpr int P = Model::P, NW = TPB / 32, NH = Tri<P>::N, V = P + NH + 2, TN = TPB * S;
   constexpr int VP = Pow2Ceil<V>::value, OWN = 32 / VP;      // transposed reduction: lane L owns value L / OWN
@@ -286,8 +295,13 @@ k_model_normal_eq_staged(const T* __restrict__ p, const T* __restrict__ x, const
     T* dst = ring + (size_t)pst * stage_elems;
     uint64_t* bar = &bars[pst];
     mbar_expect_tx(bar, bytes * (unsigned)(Cy + (has_prev ? 1 : 0)));
-    const T* src = y + pb * ybs + pn0;
-    for (int c = 0; c < Cy; ++c, src += ycs, dst += TN) bulk_g2s(dst, src, bytes, bar);
+    if (use_tm) {                                            // N % TN == 0: one tensor copy of the [Cy][TN] box (UTMALDG)
+      tma_load_3d(dst, &tmy, pn0, 0, (int)pb, bar);
+      dst += Cy * TN;
+    } else {
+      const T* src = y + pb * ybs + pn0;
+      for (int c = 0; c < Cy; ++c, src += ycs, dst += TN) bulk_g2s(dst, src, bytes, bar);
+    }
     if (has_prev) bulk_g2s(dst, (sel ? (psel ? mB : mA) : m_prev) + pb * (long long)N + pn0, bytes, bar);
     pn0 += TN;
     if (pn0 >= N) {
@@ -488,7 +502,7 @@ __global__ void __launch_bounds__(TPB, 512 / TPB)
 k_model_normal_eq_vec(const T* __restrict__ p, const T* __restrict__ x, const T* __restrict__ y, long long ybs,
                       long long ycs, const T* __restrict__ w, int wlen, long long B, int C_, int N, T* mA, T* mB,
                       T* __restrict__ g, T* __restrict__ H, double* __restrict__ stats, const nlls_ctrl* ctrl,
-                      const unsigned char* __restrict__ sel, nlls_track tr) {
+                      const unsigned char* __restrict__ sel, nlls_track tr, const __grid_constant__ CUtensorMap tmy, int use_tm) {
   if (is_done(ctrl)) return;
   constexpr int P = Model::P, NW = TPB / 32, NH = Tri<P>::N, V = P + NH + 2, VEC = Lane16<T>::VEC, TN = TPB * VEC;
   constexpr int VP = Pow2Ceil<V>::value, OWN = 32 / VP;
@@ -527,8 +541,13 @@ k_model_normal_eq_vec(const T* __restrict__ p, const T* __restrict__ x, const T*
     T* dst = ring + (size_t)pst * stage_elems;
     uint64_t* bar = &bars[pst];
     mbar_expect_tx(bar, bytes * (unsigned)(Cy + (has_prev ? 1 : 0)));
-    const T* src = y + pb * ybs + pn0;
-    for (int c = 0; c < Cy; ++c, src += ycs, dst += TN) bulk_g2s(dst, src, bytes, bar);
+    if (use_tm) {                                            // N % TN == 0: one tensor copy of the [Cy][TN] box (UTMALDG)
+      tma_load_3d(dst, &tmy, pn0, 0, (int)pb, bar);
+      dst += Cy * TN;
+    } else {
+      const T* src = y + pb * ybs + pn0;
+      for (int c = 0; c < Cy; ++c, src += ycs, dst += TN) bulk_g2s(dst, src, bytes, bar);
+    }
     if (has_prev) bulk_g2s(dst, (sel ? (psel ? mB : mA) : m_prev) + pb * (long long)N + pn0, bytes, bar);
     pn0 += TN;
     if (pn0 >= N) {
@@ -638,7 +657,7 @@ k_model_normal_eq_vec(const T* __restrict__ p, const T* __restrict__ x, const T*
     if ((lane & (OWN - 1)) == 0) myred[warp * VP + lane / OWN] = v[0];
     __syncthreads();
     if (tid == 0) issue();
-    if (tid < V) {
+    auto write_sums = [&]() {                                // threads 0 .. V-1: g, H, stats[1..2]
       double s = 0.0;
 #pragma unroll
       for (int kk = 0; kk < NW; ++kk) s += myred[kk * VP + tid];
@@ -653,7 +672,8 @@ k_model_normal_eq_vec(const T* __restrict__ p, const T* __restrict__ x, const T*
       } else {
         stats[b * 4 + (tid - P - NH) + 1] = s;
       }
-    } else if (warp == NW - 1) {
+    };
+    auto write_cost = [&]() {                                // one whole warp: sum_c (sum_n f)^2 from the per-thread sums
       const double* col = sfc + (size_t)pbuf * C * TPB;
       double tot = 0.0;
       for (int c = 0; c < C; ++c) {
@@ -667,6 +687,13 @@ k_model_normal_eq_vec(const T* __restrict__ p, const T* __restrict__ x, const T*
         stats[b * 4 + 0] = tot;
         stats[b * 4 + 3] = 0.0;
       }
+    };
+    if constexpr (NW == 1) {                                 // single-warp CTA: the same warp does both, one after the other
+      write_cost();
+      if (tid < V) write_sums();
+    } else {
+      if (tid < V) write_sums();
+      else if (warp == NW - 1) write_cost();
     }
   }
 }
@@ -1230,7 +1257,7 @@ __global__ void __launch_bounds__(TPB, MINB > 0 ? MINB : 1)
 k_model_normal_eq_gda_staged(const T* __restrict__ p, const T* __restrict__ x, const T* __restrict__ y, long long ybs,
                              long long ycs, const T* __restrict__ w, int wlen, long long B, int C_, int N, T* fsA, T* fsB,
                              double* __restrict__ g64, double* __restrict__ H64, double* __restrict__ stats,
-                             const nlls_ctrl* ctrl, nlls_track tr) {
+                             const nlls_ctrl* ctrl, nlls_track tr, const __grid_constant__ CUtensorMap tmy, int use_tm) {
   if (is_done(ctrl)) return;
   constexpr int P = Model::P, NW = TPB / 32, NH = Tri<P>::N, V = P + NH + 2, TN = TPB * S;
   constexpr int VP = Pow2Ceil<V>::value, OWN = 32 / VP;
@@ -1247,7 +1274,7 @@ k_model_normal_eq_gda_staged(const T* __restrict__ p, const T* __restrict__ x, c
   double* red = reinterpret_cast<double*>(smem_raw + Ring::bytes(Cy, 1));    // [2][NW][VP]
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   Ring R;
-  R.init(smem_raw, y, ybs, ycs, Cy, fs_prev, N, 0, 1, WL, N);
+  R.init(smem_raw, y, ybs, ycs, Cy, fs_prev, N, 0, 1, WL, N, use_tm ? &tmy : nullptr);
   int pbuf = 0;
   for (long long wi = blockIdx.x; wi < WL.n; wi += gridDim.x, pbuf ^= 1) {
     const long long b = WL.at(wi);
@@ -1573,6 +1600,41 @@ k_model_normal_eq_mma(const T* __restrict__ p, const T* __restrict__ x, const T*
 }
 
 // ------------------------------------------------------------------------------ dispatch
+// Tensor map of the data rows y viewed as [B][Cy][N] (strides y_bstride, y_cstride, 1) with a box of [1][Cy][TN]: the whole
+// data part of a tile stage arrives with ONE tensor copy instead of Cy bulk copies.  The encoder is a host-side function of the
+// driver, fetched once through the runtime (no link against libcuda); false = not available / shape not encodable.
+static bool make_rows_tensor_map(CUtensorMap* out, size_t es, const void* y, long long B, int Cy, int N, long long ybs,
+                                 long long ycs, int TN) {
+  typedef CUresult (*encode_t)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                               const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                               CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+  static encode_t encode = nullptr;
+  static int tried = 0;
+  if (!tried) {
+    tried = 1;
+    void* fn = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &q) == cudaSuccess && q == cudaDriverEntryPointSuccess)
+      encode = (encode_t)fn;
+    else
+      cudaGetLastError();
+  }
+  if (!encode || TN > 256 || Cy > 256 || ((size_t)TN * es) % 16) return false;
+  const cuuint64_t dims[3] = {(cuuint64_t)N, (cuuint64_t)Cy, (cuuint64_t)B};
+  const cuuint64_t strides[2] = {(cuuint64_t)((Cy > 1 ? ycs : (long long)N) * (long long)es), (cuuint64_t)(ybs * (long long)es)};
+  const cuuint32_t box[3] = {(cuuint32_t)TN, (cuuint32_t)Cy, 1u}, estr[3] = {1u, 1u, 1u};
+  if (strides[0] % 16 || strides[1] % 16 || strides[0] == 0 || strides[1] == 0) return false;
+  return encode(out, es == 8 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT64 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, const_cast<void*>(y), dims,
+                strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
+static int use_tensor_maps() {                                   // NLLS_TENSOR_MAP=0: keep the per-row bulk copies (A/B hook)
+  static int v = -1;
+  if (v < 0) { const char* e = getenv("NLLS_TENSOR_MAP"); v = e ? atoi(e) : 1; }
+  return v;
+}
+
 template <typename K>
 static int grid_for(K kernel, int tpb, size_t smem, long long B) {
   int per_sm = 0;
@@ -1629,10 +1691,14 @@ static int launch_staged(const ModelArgs& a) {
   const bool three = (size_t)want_ctas * (3 * stage + tail + 1024) <= 226 * 1024;
   const size_t smem2 = (three ? 3 : 2) * stage + tail;
   if (smem2 > 220 * 1024) return 1;
+  CUtensorMap tmy{};
+  const int use_tm = (a.N % TN == 0) && use_tensor_maps() && ((size_t)TN * es) % 128 == 0 &&
+                     make_rows_tensor_map(&tmy, es, a.y, a.B, Cy, a.N, a.ybs, a.ycs, TN);
   auto launch = [&](auto kern2) {
     const int grid2 = grid_for(kern2, TPB2, smem2, a.B);
     kern2<<<grid2, TPB2, smem2, a.st>>>((const T*)a.p, (const T*)a.x, (const T*)a.y, a.ybs, a.ycs, (const T*)a.w, a.wlen,
-                                        a.B, a.C, a.N, (T*)a.fA, (T*)a.fB, (T*)a.g, (T*)a.H, a.stats, a.ctrl, a.sel, a.tr);
+                                        a.B, a.C, a.N, (T*)a.fA, (T*)a.fB, (T*)a.g, (T*)a.H, a.stats, a.ctrl, a.sel, a.tr, tmy,
+                                        use_tm);
   };
   if (three) launch(k_model_normal_eq_staged<T, Model, TPB2, S2, 3, CT, MINB>);
   else launch(k_model_normal_eq_staged<T, Model, TPB2, S2, 2, CT, MINB>);
@@ -1673,15 +1739,19 @@ static int launch_vec(const ModelArgs& a) {
   const size_t tail = 16 + 64 + ((size_t)2 * NW2 * VP + (size_t)2 * a.C * TPB2) * 8;
   const bool ok16 = aligned_to(a.y, 16) && aligned_to(a.x, 16) && (a.ybs * es) % 16 == 0 && (a.ycs * es) % 16 == 0 &&
                     ((size_t)a.N * es) % 16 == 0 && (!a.fA || (aligned_to(a.fA, 16) && aligned_to(a.fB, 16)));
-  if (!ok16 || NW2 * 32 < V + 32) return 1;
+  if (!ok16 || (NW2 > 1 && NW2 * 32 < V + 32)) return 1;
   const int want_ctas = 512 / TPB2;
   const bool three = (size_t)want_ctas * (3 * stage + tail + 1024) <= 226 * 1024;
   const size_t smem2 = (three ? 3 : 2) * stage + tail;
   if (smem2 > 220 * 1024) return 1;
+  CUtensorMap tmy{};
+  const int use_tm = (a.N % TN == 0) && use_tensor_maps() && ((size_t)TN * es) % 128 == 0 &&
+                     make_rows_tensor_map(&tmy, es, a.y, a.B, Cy, a.N, a.ybs, a.ycs, TN);
   auto launch = [&](auto kern2) {
     const int grid2 = grid_for(kern2, TPB2, smem2, a.B);
     kern2<<<grid2, TPB2, smem2, a.st>>>((const T*)a.p, (const T*)a.x, (const T*)a.y, a.ybs, a.ycs, (const T*)a.w, a.wlen,
-                                        a.B, a.C, a.N, (T*)a.fA, (T*)a.fB, (T*)a.g, (T*)a.H, a.stats, a.ctrl, a.sel, a.tr);
+                                        a.B, a.C, a.N, (T*)a.fA, (T*)a.fB, (T*)a.g, (T*)a.H, a.stats, a.ctrl, a.sel, a.tr, tmy,
+                                        use_tm);
   };
   if (three) launch(k_model_normal_eq_vec<T, Model, TPB2, 3, CT>);
   else launch(k_model_normal_eq_vec<T, Model, TPB2, 2, CT>);
@@ -1738,19 +1808,20 @@ static int launch_wpp(const ModelArgs& a) {
   return check_launch("nlls_model(wpp)");
 }
 
-// fp32 default: 128-bit lanes, 64-thread CTAs, up to 8 costs as a compile-time constant
+// fp32 default: 128-bit lanes, single-warp CTAs (no CTA barrier: 21 % of the stalls of the 64-thread shape, profiles/r02n;
+// cfg-2 fp32 0.527 -> 0.486 ms, profiles/r02o), up to 8 costs as a compile-time constant
 template <typename T, typename Model>
 static int launch_vec_ct(const ModelArgs& a) {
   if constexpr (sizeof(T) == 4) {
     switch (a.C) {
-      case 1: return launch_vec<T, Model, 64, 1>(a);
-      case 2: return launch_vec<T, Model, 64, 2>(a);
-      case 3: return launch_vec<T, Model, 64, 3>(a);
-      case 4: return launch_vec<T, Model, 64, 4>(a);
-      case 5: return launch_vec<T, Model, 64, 5>(a);
-      case 6: return launch_vec<T, Model, 64, 6>(a);
-      case 7: return launch_vec<T, Model, 64, 7>(a);
-      case 8: return launch_vec<T, Model, 64, 8>(a);
+      case 1: return launch_vec<T, Model, 32, 1>(a);
+      case 2: return launch_vec<T, Model, 32, 2>(a);
+      case 3: return launch_vec<T, Model, 32, 3>(a);
+      case 4: return launch_vec<T, Model, 32, 4>(a);
+      case 5: return launch_vec<T, Model, 32, 5>(a);
+      case 6: return launch_vec<T, Model, 32, 6>(a);
+      case 7: return launch_vec<T, Model, 32, 7>(a);
+      case 8: return launch_vec<T, Model, 32, 8>(a);
       default: break;
     }
   }
@@ -1814,10 +1885,13 @@ static int launch_gda_staged(const ModelArgs& a) {
   const bool three = (size_t)want_ctas * (TileRing<T, TN, 3>::bytes(Cy, 1) + tail + 1024) <= 226 * 1024;
   const size_t smem2 = (three ? TileRing<T, TN, 3>::bytes(Cy, 1) : TileRing<T, TN, 2>::bytes(Cy, 1)) + tail;
   if (smem2 > 220 * 1024) return 1;
+  CUtensorMap tmy{};
+  const int use_tm = (a.N % TN == 0) && use_tensor_maps() && ((size_t)TN * sizeof(T)) % 128 == 0 &&
+                     make_rows_tensor_map(&tmy, sizeof(T), a.y, a.B, Cy, a.N, a.ybs, a.ycs, TN);
   auto launch = [&](auto kern2) {
     const int grid2 = grid_for(kern2, TPB2, smem2, a.B);
     kern2<<<grid2, TPB2, smem2, a.st>>>((const T*)a.p, (const T*)a.x, (const T*)a.y, a.ybs, a.ycs, (const T*)a.w, a.wlen, a.B,
-                                        a.C, a.N, (T*)a.fA, (T*)a.fB, a.g64, a.H64, a.stats, a.ctrl, a.tr);
+                                        a.C, a.N, (T*)a.fA, (T*)a.fB, a.g64, a.H64, a.stats, a.ctrl, a.tr, tmy, use_tm);
   };
   if (three) launch(k_model_normal_eq_gda_staged<T, Model, TPB2, S2, 3, CT, MINB>);
   else launch(k_model_normal_eq_gda_staged<T, Model, TPB2, S2, 2, CT, MINB>);
@@ -1864,6 +1938,8 @@ static int run_op(Op op, const ModelArgs& a) {
           case 10: rc = launch_staged<T, Model, 128, 2, 5, 3>(a); break;
           case 12: rc = launch_staged<T, Model, 64, 4, 5, 6>(a); break;       // the round-2 64 x 4 shape
           case 13: rc = launch_staged<T, Model, 32, 8, 5, 8>(a); break;
+          case 15: rc = launch_vec<T, Model, 32, 5>(a); break;                // fp32 lanes, single-warp CTAs
+          case 16: rc = launch_vec<T, Model, 128, 5>(a); break;
           case 11: rc = launch_staged<T, Model, 128, 2, 0, 0>(a); break;      // run-time C (the C > 8 kernel)
 #endif
           default:
@@ -1920,12 +1996,13 @@ static int run_op(Op op, const ModelArgs& a) {
         }
         int rc = 1;
 #ifndef NLLS_USER_MODEL_HEADER
-        if (fused_variant() == 5) rc = launch_cost_vec<T, Model, 128>(a);
+        if (fused_variant() == 15) rc = launch_cost_vec<T, Model, 32>(a);
+        else if (fused_variant() == 5) rc = launch_cost_vec<T, Model, 128>(a);
         else if (fused_variant() == 7) rc = launch_cost_vec<T, Model, 256>(a);
         else if (fused_variant() == 6) rc = launch_cost_vec<T, Model, 64>(a);
         else
 #endif
-        if (vec_family<T>()) rc = launch_cost_vec<T, Model, 64>(a);
+        if (vec_family<T>()) rc = a.C <= 8 ? launch_cost_vec<T, Model, 32>(a) : launch_cost_vec<T, Model, 64>(a);
         // same sample-to-thread map as the normal-equation kernel of the same shape (launch_staged_ct): the two-pass and
         // the speculative LM schedules see the same bits in stats[0]
         if (rc == 1 && sizeof(T) == 8 && a.C <= 8) rc = launch_cost_staged<T, Model, 32, 4>(a);
