@@ -210,6 +210,26 @@ int nlls_model_normal_eq(int model, int dtype, const void* p, int P, const void*
                          void* m_pp0, void* m_pp1, void* g, void* H, double* stats,
                          const nlls_ctrl* ctrl, const nlls_track* track /*nullable*/, void* stream);
 
+/* nlls_model_normal_eq_static: nlls_model_normal_eq for callers that cannot allocate device memory (code under CUDA graph
+ * capture, serving loops, harnesses that forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.
+ * The two [B,N] model-value ping-pong buffers (m_pp0 / m_pp1 above — the kernel's scratch) live in a
+ * file-scope static __device__ array of the library (csrc/static_scratch.cu): 2 x NLLS_STATIC_SCRATCH_ELEMS x 8 bytes = 16 MiB
+ * on every GPU that loads the library, held until the process exits.  The caller passes inputs and outputs only; everything else
+ * (arguments, outputs, iteration parity from ctrl->iters, error codes) is nlls_model_normal_eq's, and the results are bit-identical.
+ *   limit   B * N <= NLLS_STATIC_SCRATCH_ELEMS for either dtype; beyond it the call returns NLLS_E_SHAPE with a message.
+ *   allocs  none: no cudaMalloc / cudaFree / allocating library routine.  The first call on each device looks the array's device
+ *           address up (cudaGetSymbolAddress, with that device current) — make that first call outside stream capture.
+ *   sharing every call on a device uses the SAME array, and the array keeps the last call's contents: iteration k > 0 reads the
+ *           model values that the previous call (iteration k-1 of the same batch) left there; iteration 0 reads nothing, so
+ *           nothing has to be cleared.  Calls that overlap on the GPU (two streams, two host threads, two solves interleaved
+ *           iteration by iteration) RACE on it: one solve at a time per device. */
+#define NLLS_STATIC_SCRATCH_ELEMS 1048576LL
+int nlls_model_normal_eq_static(int model, int dtype, const void* p, int P, const void* x, const void* y,
+                                long long y_bstride, long long y_cstride,
+                                const void* wvec, int wlen, long long B, int C, int N,
+                                void* g, void* H, double* stats,
+                                const nlls_ctrl* ctrl, const nlls_track* track /*nullable*/, void* stream);
+
 /* Speculative Levenberg-Marquardt trial evaluation (fused path): ONE pass at the trial point p + h that yields
  * both halves of what lma:99-100 and the NEXT iteration's newton_parallel.py:38-43 need:
  *   stats_t[b] = { sum_c (sum_n f_t)^2  (trial cost of the gain ratio, lma:100),

@@ -30,7 +30,7 @@ class Track(ctypes.Structure):
 _tp = ctypes.POINTER(Track)
 # entry points that take `const nlls_track* track` as their last argument before `stream`; call() inserts it (track=None: none)
 TRACKED = ('nlls_lm_solve', 'nlls_lm_update', 'nlls_gn_update', 'nlls_gd_update', 'nlls_iter_end', 'nlls_model_normal_eq',
-           'nlls_model_normal_eq_gda', 'nlls_model_lm_trial', 'nlls_lm_update_spec')
+           'nlls_model_normal_eq_gda', 'nlls_model_lm_trial', 'nlls_lm_update_spec', 'nlls_model_normal_eq_static')
 
 # name -> argtypes; mirrors include/nlls_b200.h one to one (tests check the exported symbols)
 SIGNATURES = {
@@ -50,6 +50,7 @@ SIGNATURES = {
     'nlls_sumsq': [_i, _vp, _vp, _ll, _vp, _vp],
     'nlls_model_eval': [_i, _i, _vp, _i, _vp, _vp, _ll, _ll, _ll, _i, _i, _vp, _vp, _vp, _vp],
     'nlls_model_normal_eq': [_i, _i, _vp, _i, _vp, _vp, _ll, _ll, _vp, _i, _ll, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _tp, _vp],
+    'nlls_model_normal_eq_static': [_i, _i, _vp, _i, _vp, _vp, _ll, _ll, _vp, _i, _ll, _i, _i, _vp, _vp, _vp, _vp, _tp, _vp],
     'nlls_model_normal_eq_gda': [_i, _i, _vp, _i, _vp, _vp, _ll, _ll, _vp, _i, _ll, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _tp, _vp],
     'nlls_model_cost_stat': [_i, _i, _vp, _i, _vp, _vp, _ll, _ll, _ll, _i, _i, _vp, _vp, _vp],
     'nlls_model_lm_trial': [_i, _i, _vp, _i, _vp, _vp, _ll, _ll, _vp, _i, _ll, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _tp, _vp],
