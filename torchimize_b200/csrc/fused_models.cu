@@ -1938,6 +1938,10 @@ static int run_op(Op op, const ModelArgs& a) {
           case 10: rc = launch_staged<T, Model, 128, 2, 5, 3>(a); break;
           case 12: rc = launch_staged<T, Model, 64, 4, 5, 6>(a); break;       // the round-2 64 x 4 shape
           case 13: rc = launch_staged<T, Model, 32, 8, 5, 8>(a); break;
+          case 17: rc = launch_staged<T, Model, 32, 4, 5, 16>(a); break;      // 128 registers: 16 single-warp CTAs per SM
+          case 18: rc = launch_staged<T, Model, 32, 2, 5, 16>(a); break;
+          case 19: rc = launch_staged<T, Model, 32, 2, 5, 20>(a); break;      // 96 registers: 20 per SM
+          case 20: rc = launch_staged<T, Model, 32, 4, 5, 14>(a); break;      // 144 registers: 14 per SM
           case 15: rc = launch_vec<T, Model, 32, 5>(a); break;                // fp32 lanes, single-warp CTAs
           case 16: rc = launch_vec<T, Model, 128, 5>(a); break;
           case 11: rc = launch_staged<T, Model, 128, 2, 0, 0>(a); break;      // run-time C (the C > 8 kernel)

@@ -33,29 +33,50 @@ __device__ __forceinline__ float ex2_approx(float x) {
 template <typename T> struct ExpNeg;
 // fp64 exp for NON-POSITIVE arguments (every call site below evaluates exp(-a), a >= 0).  CUDA's exp() costs ~30
 // instructions plus ~20 moves that materialise its polynomial constants as immediates (IMAD.MOV was 18 % of the warp
-// instructions of the fp64 fused kernel, profiles/r01h_fused_ncu.txt); here the coefficients sit in constant memory, so
-// every DFMA reads its coefficient as a c[bank][offset] operand.  Cody-Waite reduction x = n ln2 + r, |r| <= ln2/2,
-// degree-13 Taylor polynomial (remainder < 5e-18 relative), scaling by 2^n through the exponent field; < 1 ulp measured
-// against torch.exp (tests/test_gpu_parity.py::test_fp64_exp_nonpos_accuracy).  Results below 2^-1020 (x < -707) are
-// flushed to 0: the reference's denormal tail (< 1e-307) is absolutely negligible in every sum it enters.  NaN propagates.
-__constant__ double kExpTaylor[12] = {1.6059043836821613e-10, 2.08767569878681e-09, 2.505210838544172e-08, 2.755731922398589e-07,
-                                      2.7557319223985893e-06, 2.48015873015873e-05, 0.0001984126984126984, 0.001388888888888889,
-                                      0.008333333333333333, 0.041666666666666664, 0.16666666666666666, 0.5};
+// instructions of the fp64 fused kernel, profiles/r01h_fused_ncu.txt).  Table-driven: x = (32 k + j) ln2/32 + r with
+// |r| <= ln2/64 (Cody-Waite, the high part of ln2/32 has 24 trailing zero bits so t*hi is exact), exp(x) = 2^k * T[j] * (1 + p(r))
+// with p of degree 6 (remainder < 4e-18 relative) and T[j] = 2^(j/32) as a hi + lo pair (one 16-byte load from a 512-byte
+// table that stays in L1): 12 FP64 instructions with a 7-deep dependent chain instead of the 18 / 16-deep of a degree-13
+// polynomial on |r| <= ln2/2.  0.55 ulp worst case over [-700, 0] (C model of the same fma sequence against expl; on the GPU:
+// tests/test_gpu_parity.py::test_fp64_exp_nonpos_accuracy).  Results below 2^-1020 (x < -707) are flushed to 0: the
+// reference's denormal tail (< 1e-307) is absolutely negligible in every sum it enters.  NaN propagates.
+__device__ __align__(512) const double2 kExp2Tab[32] = {
+    {1.0, 0.0}, {1.0218971486541166, 5.109225028973444e-17},
+    {1.0442737824274138, 8.551889705537965e-17}, {1.0671404006768237, -7.899853966841582e-17},
+    {1.0905077326652577, -3.046782079812471e-17}, {1.1143867425958924, 1.0410278456845571e-16},
+    {1.1387886347566916, 8.912812676025408e-17}, {1.1637248587775775, 3.8292048369240935e-17},
+    {1.189207115002721, 3.982015231465646e-17}, {1.215247359980469, -7.712630692681488e-17},
+    {1.241857812073484, 4.658027591836937e-17}, {1.2690509571917332, 2.667932131342186e-18},
+    {1.2968395546510096, 2.5382502794888315e-17}, {1.3252366431597413, -2.8587312100388614e-17},
+    {1.3542555469368927, 7.70094837980299e-17}, {1.383909881963832, -6.770511658794786e-17},
+    {1.4142135623730951, -9.667293313452913e-17}, {1.4451808069770467, -3.0237581349939873e-17},
+    {1.4768261459394993, -3.483994556892796e-17}, {1.5091644275934228, -1.016455327754295e-16},
+    {1.5422108254079407, 7.949834809697621e-17}, {1.5759808451078865, -1.0136916471278304e-17},
+    {1.6104903319492543, 2.4707192569797888e-17}, {1.645755478153965, -1.0125679913674773e-16},
+    {1.681792830507429, 8.199010020581497e-17}, {1.718619298122478, -1.851380418263111e-17},
+    {1.7562521603732995, 2.960140695448873e-17}, {1.7947090750031072, 1.8227458427912087e-17},
+    {1.8340080864093424, 3.283107224245627e-17}, {1.8741676341103, -6.122763413004143e-17},
+    {1.9152065613971474, -1.0619946056195963e-16}, {1.9571441241754002, 8.960767791036668e-17}};
+__constant__ double kExpPoly[5] = {0.001388888888888889, 0.008333333333333333, 0.041666666666666664, 0.16666666666666666, 0.5};
 // Branch-free (the flush and the NaN case are selects at the end): several calls in one basic block — the two exps of a
-// sample, the samples of a thread — interleave their 14-deep Horner chains instead of running one after the other.
+// sample, the samples of a thread — interleave their dependent chains instead of running one after the other.
 __device__ __forceinline__ double exp_nonpos(double x) {
-  const double magic = 6755399441055744.0;                   // 1.5 * 2^52: fma rounds x*log2(e) to the nearest integer
-  double t = fma(x, 1.4426950408889634, magic);
-  const int n = __double2loint(t);
+  const double magic = 6755399441055744.0;                   // 1.5 * 2^52: fma rounds x*32/ln2 to the nearest integer
+  double t = fma(x, 46.16624130844683, magic);
+  const int n = __double2loint(t);                           // 32 k + j (two's complement: j = n & 31, k = n >> 5)
   t -= magic;
-  double r = fma(t, -0.6931471803691238, x);                 // ln2 split: high part has 21 trailing zero bits (t*hi exact)
-  r = fma(t, -1.9082149292705877e-10, r);
-  double q = kExpTaylor[0];
+  // entry j of the 512-byte aligned table: base | (j * 16) — ONE logic op on the low address word, no 64-bit add; the index is
+  // masked, so the load is in range whatever x was
+  const double2 T = __ldg(reinterpret_cast<const double2*>(reinterpret_cast<unsigned long long>(kExp2Tab) |
+                                                           (unsigned long long)(unsigned)((n << 4) & 0x1f0)));
+  double r = fma(t, -0.021660849335603416, x);
+  r = fma(t, -5.689487495325457e-11, r);
+  double q = fma(r, kExpPoly[0], kExpPoly[1]);
 #pragma unroll
-  for (int i = 1; i < 12; ++i) q = fma(q, r, kExpTaylor[i]);
-  q = fma(q, r, 1.0);
-  q = fma(q, r, 1.0);
-  const double e = __hiloint2double(__double2hiint(q) + (n << 20), __double2loint(q));
+  for (int i = 2; i < 5; ++i) q = fma(q, r, kExpPoly[i]);
+  const double p = fma(q, r * r, r);                         // exp(r) - 1
+  const double m = fma(T.x, p, T.y) + T.x;
+  const double e = __hiloint2double(__double2hiint(m) + ((n >> 5) << 20), __double2loint(m));
   return x >= -707.0 ? e : (x < -707.0 ? 0.0 : x);          // flushed tail; NaN propagates
 }
 template <> struct ExpNeg<double> {
@@ -73,20 +94,53 @@ template <> __device__ __forceinline__ double t_erf<double>(double x) { return e
 template <> __device__ __forceinline__ float t_erf<float>(float x) { return erff(x); }
 
 // K(x) = 1 + erf(x) given E = exp(-x^2).
-//   fp64: CUDA's erf (the 1e-9 parity target needs full accuracy).
+//   fp64: |x| >= 6 exits early (below); else erfc(|x|) = E * g(|x|) with the scaled complementary error function g = erfcx as
+//         ONE polynomial of degree 20 in s = 1 - 3 v, v = |x| / (|x| + 3)  (x in [0, 6] <-> s in [-1, 1]; Chebyshev
+//         interpolant converted to the monomial basis, approximation error 3.4e-19 relative; coefficients decay like 0.23^j,
+//         so Horner in s is well conditioned), K = erfc(|x|) for x < 0 and 2 - erfc(x) otherwise.  v = |x| * rcp(|x| + 3) keeps
+//         RELATIVE accuracy near x = 0 (forming s from the reciprocal directly would amplify its rounding 9-fold).  The
+//         reciprocal is MUFU.RCP64H + two Newton steps (|x| + 3 is in [3, 9]: no special cases, no slow-path call).
+//         C model of the same fma sequence against erfl / erfcl over [-6, 6]: 1.6 ulp worst for x >= 0, absolute error
+//         < 2.6e-16 for x < 0 (CUDA's erf: 2 ulp; the reference's own 1 + erf(x) for x < 0: 1e-16 absolute).  36 instructions,
+//         coefficients read from constant memory, instead of CUDA erf's ~125 (of which ~60 moves that materialise its
+//         polynomial constants, an exp of its own and a division with a slow path): profiles/r02r.
 //   fp32: branch-free  erfc(|x|) = E * t * Q(t),  t = 1 / (1 + 0.3 |x|),  Q of degree 8 fitted to the scaled
 //         complementary error function erfcx on [0, 10.5] (max relative error 2.0e-8 in exact arithmetic,
 //         4.3e-7 evaluated in fp32); K = erfc(|x|) for x < 0 (no cancellation: relative accuracy in the
 //         left tail, where the reference's own fp32 `1 + erf(x)` rounds to 0) and 2 - erfc(x) otherwise.
 //         ~16 instructions and no divergent branch instead of erff's two-sided ~40, and E is needed for
 //         the derivative anyway.  Fit: least squares with Lawson reweighting on the relative error.
+__constant__ double kErfcxPoly[21] = {
+    0.3215854164543175, 0.3681515648982602, 0.20143885681922427, 0.08162684513404136,
+    0.023308261232669675, 0.003956151636369144, 7.012531316823998e-05, -0.00012716419852449776,
+    -1.5153799232302407e-05, 4.5326059043145345e-06, 8.118056744135089e-07, -2.2754311847571347e-07,
+    -3.480551916961012e-08, 1.4460927996927543e-08, 8.288178726793465e-10, -9.443620513901106e-10,
+    6.175705066293916e-11, 5.1980047888428754e-11, -1.1416522779737793e-11, -1.7471767934261753e-12,
+    8.081438420827511e-13};
+// erfc-based core for |x| < 6 (NaN falls through it and comes out as NaN)
+__device__ __forceinline__ double one_plus_erf_core(double x, double E) {
+  const double ax = fabs(x);
+  const double w = ax + 3.0;
+  double r;
+  asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(w));
+  double e = fma(-w, r, 1.0);
+  r = fma(r, e, r);
+  e = fma(-w, r, 1.0);
+  r = fma(r, e, r);
+  const double s = fma(-3.0, ax * r, 1.0);
+  double g = kErfcxPoly[20];
+#pragma unroll
+  for (int i = 19; i >= 0; --i) g = fma(g, s, kErfcxPoly[i]);
+  const double c = E * g;                                     // erfc(|x|)
+  return x < 0.0 ? c : 2.0 - c;
+}
 template <typename T> __device__ __forceinline__ T one_plus_erf(T x, T E);
-template <> __device__ __forceinline__ double one_plus_erf<double>(double x, double) {
+template <> __device__ __forceinline__ double one_plus_erf<double>(double x, double E) {
   // |x| >= 6: 1 - erf(|x|) < 2.2e-17 < 2^-54, so erf rounds to +-1 exactly and 1 + erf(x) is exactly 2 or 0 — the value
   // the reference's torch.erf produces.  Samples are adjacent along the abscissa, so whole warps take this exit in the
-  // tails of a peak (86 % of the samples of the EMG workloads) and skip CUDA's erf (~90 instructions, one division).
+  // tails of a peak (82 % of the warp-samples of the EMG workloads).
   if (fabs(x) >= 6.0) return x > 0.0 ? 2.0 : 0.0;
-  return 1.0 + erf(x);
+  return one_plus_erf_core(x, E);
 }
 template <> __device__ __forceinline__ float one_plus_erf<float>(float x, float E) {
   const float ax = fabsf(x);
@@ -103,6 +157,13 @@ template <> __device__ __forceinline__ float one_plus_erf<float>(float x, float 
   q = fmaf(q, t, 0.1691874673196955f);
   const float c = E * (t * q);                    // erfc(|x|)
   return x < 0.0f ? c : 2.0f - c;
+}
+// value()-only form (no derivative needs E): fp64 evaluates exp(-x^2) inside the |x| < 6 branch only — the SAME expression
+// eval()'s phase 1 forms, so the model value is bit-identical between value() and eval().
+template <typename T> __device__ __forceinline__ T one_plus_erf_lazy(T x) { return one_plus_erf<T>(x, ExpNeg<T>::sq(x)); }
+template <> __device__ __forceinline__ double one_plus_erf_lazy<double>(double x) {
+  if (fabs(x) >= 6.0) return x > 0.0 ? 2.0 : 0.0;
+  return one_plus_erf_core(x, ExpNeg<double>::sq(x));
 }
 
 template <typename T>
@@ -121,9 +182,7 @@ struct EmgModel {
     const T d = t - mu;
     const T G = ExpNeg<T>::eval(d * d, inv_s2h);                 // gauss_term, emg.py:20
     const T x = xs * d;
-    T E = T(0);
-    if constexpr (sizeof(T) == 4) E = ExpNeg<T>::sq(x);
-    const T A = one_plus_erf<T>(x, E);                        // asymm_term, emg.py:21
+    const T A = one_plus_erf_lazy<T>(x);                      // asymm_term, emg.py:21
     return alpha * (G * A);                                   // same association as eval(): bit-identical m
   }
   // eval() in three phases, so that callers with several evaluations in flight (the samples of a thread, the peaks of a
@@ -230,9 +289,7 @@ struct SkewGaussModel {
     const T d = t - mean;
     const T S = ExpNeg<T>::eval(d * d, inv_s2h);                 // :48
     const T x = xs * d;
-    T E = T(0);
-    if constexpr (sizeof(T) == 4) E = ExpNeg<T>::sq(x);
-    const T K = one_plus_erf<T>(x, E);                        // :49
+    const T K = one_plus_erf_lazy<T>(x);                      // :49
     return amp * (S * K) + off;                               // same association as eval()
   }
   __device__ __forceinline__ void eval(T t, T& m, T (&k)[P]) const {
