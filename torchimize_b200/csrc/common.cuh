@@ -205,6 +205,22 @@ __device__ __forceinline__ void tma_load_3d(void* dst_smem, const CUtensorMap* t
       : "memory");
 }
 
+// The same three operations on 32-bit shared-window addresses (smem_u32) the caller computed once: a producer that issues a
+// copy per tile keeps `ring` and `bars` as two integers instead of converting generic pointers on every tile.
+__device__ __forceinline__ void mbar_expect_tx_s(uint32_t bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s_s(uint32_t dst, const void* src_gmem, uint32_t bytes, uint32_t bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst), "l"(src_gmem),
+               "r"(bytes), "r"(bar)
+               : "memory");
+}
+__device__ __forceinline__ void tma_load_3d_s(uint32_t dst, const CUtensorMap* tm, int c0, int c1, int c2, uint32_t bar) {
+  asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];" ::"r"(dst),
+               "l"(tm), "r"(c0), "r"(c1), "r"(c2), "r"(bar)
+               : "memory");
+}
+
 // ------------------------------------------------------------------ small dense fp64 solves
 // Solve A x = b for a symmetric P x P system held fully in registers (A is destroyed).
 // Cholesky first; if a pivot is not strictly positive (or not finite) the original matrix is

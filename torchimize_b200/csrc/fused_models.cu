@@ -284,33 +284,47 @@ k_model_normal_eq_staged(const T* __restrict__ p, const T* __restrict__ x, const
   }
   __syncthreads();
 
-  // ---- producer state (thread 0): next tile to issue = (problem pb, sample offset pn0) into stage pst
+  // ---- producer state (thread 0): next tile to issue = (problem pb, sample offset pn0) into stage pst.  Everything that
+  // changes only with the problem (its previous-model row) or never (shared-window addresses, the byte count of a full tile)
+  // is kept in registers: the per-tile path is two adds, the barrier arm and the copies.
   long long pw = blockIdx.x, pb = pw < WL.n ? WL.at(pw) : 0;   // producer: work index, problem
-  int pn0 = 0, pst = 0;
+  int pn0 = 0;
   unsigned char psel = (sel && tid == 0 && pw < WL.n) ? sel[pb] : (unsigned char)0;
+  const uint32_t ring_s = smem_u32(ring), bars_s = smem_u32(bars);
+  constexpr uint32_t kTileBytes = (uint32_t)TN * (uint32_t)sizeof(T);
+  const uint32_t stage_bytes = (uint32_t)stage_elems * (uint32_t)sizeof(T);
+  const uint32_t full_tx = kTileBytes * (uint32_t)(Cy + (has_prev ? 1 : 0));
+  uint32_t pdst = ring_s, pbar = bars_s;                       // stage pst: data address, barrier address
+  int pst = 0;
+  auto prev_row = [&]() -> const T* {                          // previous model values of problem pb (sel: its own buffer role)
+    return has_prev ? (sel ? (psel ? mB : mA) : m_prev) + pb * (long long)N : nullptr;
+  };
+  const T* msrc = prev_row();
   auto issue = [&]() {
     if (pw >= WL.n) return;
-    const int rows = min(TN, N - pn0);
-    const unsigned bytes = (unsigned)rows * (unsigned)sizeof(T);
-    T* dst = ring + (size_t)pst * stage_elems;
-    uint64_t* bar = &bars[pst];
-    mbar_expect_tx(bar, bytes * (unsigned)(Cy + (has_prev ? 1 : 0)));
-    if (use_tm) {                                            // N % TN == 0: one tensor copy of the [Cy][TN] box (UTMALDG)
-      tma_load_3d(dst, &tmy, pn0, 0, (int)pb, bar);
-      dst += Cy * TN;
+    if (use_tm) {                                            // N % TN == 0: every tile is full; one tensor copy of the [Cy][TN] box
+      mbar_expect_tx_s(pbar, full_tx);
+      tma_load_3d_s(pdst, &tmy, pn0, 0, (int)pb, pbar);
+      if (has_prev) bulk_g2s_s(pdst + (uint32_t)Cy * kTileBytes, msrc + pn0, kTileBytes, pbar);
     } else {
+      const int rows = min(TN, N - pn0);
+      const unsigned bytes = (unsigned)rows * (unsigned)sizeof(T);
+      mbar_expect_tx_s(pbar, bytes * (unsigned)(Cy + (has_prev ? 1 : 0)));
       const T* src = y + pb * ybs + pn0;
-      for (int c = 0; c < Cy; ++c, src += ycs, dst += TN) bulk_g2s(dst, src, bytes, bar);
+      uint32_t dst = pdst;
+      for (int c = 0; c < Cy; ++c, src += ycs, dst += kTileBytes) bulk_g2s_s(dst, src, bytes, pbar);
+      if (has_prev) bulk_g2s_s(dst, msrc + pn0, bytes, pbar);
     }
-    if (has_prev) bulk_g2s(dst, (sel ? (psel ? mB : mA) : m_prev) + pb * (long long)N + pn0, bytes, bar);
     pn0 += TN;
     if (pn0 >= N) {
       pn0 = 0;
       pw += gridDim.x;
       pb = pw < WL.n ? WL.at(pw) : 0;
       if (sel && pw < WL.n) psel = sel[pb];                     // buffer role of the NEXT problem: in flight until its first tile
+      msrc = prev_row();
     }
-    pst = (pst + 1 == NSTAGE) ? 0 : pst + 1;
+    if (++pst == NSTAGE) { pst = 0; pdst = ring_s; pbar = bars_s; }
+    else { pdst += stage_bytes; pbar += 8; }
   };
   if (tid == 0) {
 #pragma unroll
@@ -396,7 +410,8 @@ k_model_normal_eq_staged(const T* __restrict__ p, const T* __restrict__ x, const
       if (n0 + TN <= N) tile(n0, std::true_type{});
       else tile(n0, std::false_type{});
       if (n0 + TN < N) {
-        __syncthreads();                                     // every thread is done with this stage
+        if constexpr (NW == 1) __syncwarp();                 // every thread is done with this stage (one warp: no CTA barrier)
+        else __syncthreads();
         if (tid == 0) issue();
       }
       if (++st == NSTAGE) { st = 0; ph ^= 1u; }
@@ -1938,10 +1953,6 @@ static int run_op(Op op, const ModelArgs& a) {
           case 10: rc = launch_staged<T, Model, 128, 2, 5, 3>(a); break;
           case 12: rc = launch_staged<T, Model, 64, 4, 5, 6>(a); break;       // the round-2 64 x 4 shape
           case 13: rc = launch_staged<T, Model, 32, 8, 5, 8>(a); break;
-          case 17: rc = launch_staged<T, Model, 32, 4, 5, 16>(a); break;      // 128 registers: 16 single-warp CTAs per SM
-          case 18: rc = launch_staged<T, Model, 32, 2, 5, 16>(a); break;
-          case 19: rc = launch_staged<T, Model, 32, 2, 5, 20>(a); break;      // 96 registers: 20 per SM
-          case 20: rc = launch_staged<T, Model, 32, 4, 5, 14>(a); break;      // 144 registers: 14 per SM
           case 15: rc = launch_vec<T, Model, 32, 5>(a); break;                // fp32 lanes, single-warp CTAs
           case 16: rc = launch_vec<T, Model, 128, 5>(a); break;
           case 11: rc = launch_staged<T, Model, 128, 2, 0, 0>(a); break;      // run-time C (the C > 8 kernel)
