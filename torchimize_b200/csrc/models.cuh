@@ -29,7 +29,7 @@ __device__ __forceinline__ float ex2_approx(float x) {
   return r;
 }
 // exp(-a c) for a >= 0 with a per-problem constant c prepared once: fp32 folds the sign and log2(e) into the constant
-// (ONE FMUL + MUFU.EX2 per evaluation, no negation instruction); fp64 keeps CUDA's exp on the exactly negated product.
+// (ONE FMUL + MUFU.EX2 per evaluation, no negation instruction); fp64 evaluates exp_nonpos (below) on the exactly negated product.
 template <typename T> struct ExpNeg;
 // fp64 exp for NON-POSITIVE arguments (every call site below evaluates exp(-a), a >= 0).  CUDA's exp() costs ~30
 // instructions plus ~20 moves that materialise its polynomial constants as immediates (IMAD.MOV was 18 % of the warp
@@ -101,7 +101,7 @@ template <> __device__ __forceinline__ float t_erf<float>(float x) { return erff
 //         RELATIVE accuracy near x = 0 (forming s from the reciprocal directly would amplify its rounding 9-fold).  The
 //         reciprocal is MUFU.RCP64H + two Newton steps (|x| + 3 is in [3, 9]: no special cases, no slow-path call).
 //         C model of the same fma sequence against erfl / erfcl over [-6, 6]: 1.6 ulp worst for x >= 0, absolute error
-//         < 2.6e-16 for x < 0 (CUDA's erf: 2 ulp; the reference's own 1 + erf(x) for x < 0: 1e-16 absolute).  36 instructions,
+//         < 2.6e-16 for x < 0 (CUDA's erf: 2 ulp; the reference's own 1 + erf(x) for x < 0: 1e-16 absolute).  48 instructions,
 //         coefficients read from constant memory, instead of CUDA erf's ~125 (of which ~60 moves that materialise its
 //         polynomial constants, an exp of its own and a division with a slow path): profiles/r02r.
 //   fp32: branch-free  erfc(|x|) = E * t * Q(t),  t = 1 / (1 + 0.3 |x|),  Q of degree 8 fitted to the scaled
