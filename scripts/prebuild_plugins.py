@@ -16,13 +16,21 @@ MODELS = {
     'emg2_clone': 'namespace nlls { template <typename T> struct UserModel : MultiEmgModel<T, 2> {}; }\n',
 }
 
-if __name__ == '__main__':
+def build_all(prune=True):
+    """compile the three plugins in parallel (cached by source hash); prune: drop builds of older kernel sources"""
     import shutil
-    keep = set()
+    keep, built = set(), []
     with ThreadPoolExecutor(len(MODELS)) as ex:
         for so in ex.map(lambda kv: _lib.build_plugin(kv[1], kv[0]), MODELS.items()):
-            print('built', os.path.relpath(so, ROOT))
+            built.append(so)
             keep.add(os.path.basename(os.path.dirname(so)))
-    for d in os.listdir(_lib.JIT_DIR):                               # builds of older kernel sources: dead weight in the snapshot
-        if d not in keep:
-            shutil.rmtree(os.path.join(_lib.JIT_DIR, d), ignore_errors=True)
+    if prune:
+        for d in os.listdir(_lib.JIT_DIR):                           # builds of older kernel sources: dead weight in the snapshot
+            if d not in keep:
+                shutil.rmtree(os.path.join(_lib.JIT_DIR, d), ignore_errors=True)
+    return built
+
+
+if __name__ == '__main__':
+    for so in build_all():
+        print('built', os.path.relpath(so, ROOT))
