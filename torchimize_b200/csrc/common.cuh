@@ -115,6 +115,16 @@ template <int V> struct Pow2Ceil { static constexpr int value = V <= 1 ? 1 : V <
 
 // product rounded on its own (never contracted into an FMA): the reference materialises f = r*r before summing it,
 // and every kernel that evaluates the same residual has to produce the same bits whatever the compiler fuses
+// Packed fp32 pairs (sm_100: add / mul / fma .f32x2 -> SASS FADD2 / FMUL2 / FFMA2): ONE issue slot for two lanes' worth of fp32
+// arithmetic, each lane rounded exactly like the scalar instruction (the multiply is never contracted).  Same flop rate as
+// the scalar pipe; what it saves is instruction issue, which is what bounds the fp32 fused kernels.
+struct f32x2 { unsigned long long v; };
+__device__ __forceinline__ f32x2 pack2(float lo, float hi) { f32x2 r; asm("mov.b64 %0, {%1, %2};" : "=l"(r.v) : "f"(lo), "f"(hi)); return r; }
+__device__ __forceinline__ void unpack2(f32x2 a, float& lo, float& hi) { asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(a.v)); }
+__device__ __forceinline__ f32x2 add2(f32x2 a, f32x2 b) { f32x2 r; asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r.v) : "l"(a.v), "l"(b.v)); return r; }
+__device__ __forceinline__ f32x2 mul2(f32x2 a, f32x2 b) { f32x2 r; asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r.v) : "l"(a.v), "l"(b.v)); return r; }
+__device__ __forceinline__ f32x2 fma2(f32x2 a, f32x2 b, f32x2 c) { f32x2 r; asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r.v) : "l"(a.v), "l"(b.v), "l"(c.v)); return r; }
+__device__ __forceinline__ f32x2 neg2(f32x2 a) { f32x2 r; r.v = a.v ^ 0x8000000080000000ull; return r; }
 __device__ __forceinline__ double mul_rn(double a, double b) { return __dmul_rn(a, b); }
 __device__ __forceinline__ float mul_rn(float a, float b) { return __fmul_rn(a, b); }
 
